@@ -1,0 +1,501 @@
+// Coalesced, vectorised elementwise / row-reduction kernels of the FiT hot path (family 3 and 4 of
+// SURVEY.md section 8): mask scan, patchify+embed, timestep sinusoid, conditioning combine,
+// LayerNorm+modulate, final layer (+unpatchify), fused CFG + DDPM/DDIM step, q_sample.
+// All HBM-bound: one pass over the data, 16-byte accesses, fp32 math.
+#include <cstdarg>
+
+#include "common.cuh"
+
+namespace fitb200 {
+
+static thread_local char g_err[512] = "";
+void set_last_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// --------------------------------------------------------------------------------------------
+// mask -> kv_len / n_valid : one warp per sample
+// --------------------------------------------------------------------------------------------
+__global__ void mask_to_kvlen_kernel(const uint8_t* __restrict__ mask, int R, int T, int32_t* __restrict__ kv_len,
+                                     int32_t* __restrict__ n_valid) {
+  int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (r >= R) return;
+  int last = 0, cnt = 0;
+  for (int j = lane; j < T; j += 32) {
+    if (mask[(size_t)r * T + j]) { last = j + 1; ++cnt; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  if (lane == 0) {
+    kv_len[r] = last;
+    if (n_valid) n_valid[r] = cnt;
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// patchify + x_embedder.  CTA: TOK tokens x 128 output columns.
+// --------------------------------------------------------------------------------------------
+constexpr int EMB_TOK = 32;
+
+template <typename OutT>
+__global__ void __launch_bounds__(128) embed_tokens_kernel(const float* __restrict__ x, int nchw, int R, int R_src, int C,
+                                                           int H, int W, int p, int T, const float* __restrict__ w,
+                                                           const float* __restrict__ b, int D, OutT* __restrict__ out) {
+  extern __shared__ float xs[];  // [EMB_TOK][K]
+  const int K = p * p * C;
+  const long tok0 = (long)blockIdx.x * EMB_TOK;
+  const long ntok = (long)R * T;
+  const int nw = nchw ? (W / p) : 0;
+  for (int i = threadIdx.x; i < EMB_TOK * K; i += blockDim.x) {
+    int tl = i / K, k = i - tl * K;
+    long tok = tok0 + tl;
+    float v = 0.f;
+    if (tok < ntok) {
+      int r = (int)(tok / T), tk = (int)(tok - (long)r * T);
+      int rs = r % R_src;
+      if (nchw) {
+        int ih = tk / nw, iw = tk - ih * nw;
+        int c = k % C, pp = k / C;
+        int ph = pp / p, pw = pp - ph * p;
+        v = x[(((size_t)rs * C + c) * H + (ih * p + ph)) * W + (iw * p + pw)];
+      } else {
+        v = x[((size_t)rs * T + tk) * K + k];
+      }
+    }
+    xs[i] = v;
+  }
+  __syncthreads();
+  const int j = blockIdx.y * 128 + threadIdx.x;
+  if (j >= D) return;
+  float acc[EMB_TOK];
+  const float bj = b[j];
+#pragma unroll
+  for (int t = 0; t < EMB_TOK; ++t) acc[t] = bj;
+  for (int k0 = 0; k0 < K; k0 += 4) {
+    float4 wv = *reinterpret_cast<const float4*>(w + (size_t)j * K + k0);
+#pragma unroll
+    for (int t = 0; t < EMB_TOK; ++t) {
+      const float* xr = xs + t * K + k0;
+      acc[t] = fmaf(wv.x, xr[0], acc[t]);
+      acc[t] = fmaf(wv.y, xr[1], acc[t]);
+      acc[t] = fmaf(wv.z, xr[2], acc[t]);
+      acc[t] = fmaf(wv.w, xr[3], acc[t]);
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < EMB_TOK; ++t) {
+    long tok = tok0 + t;
+    if (tok < ntok) out[(size_t)tok * D + j] = from_f32<OutT>(acc[t]);
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// timestep sinusoid
+// --------------------------------------------------------------------------------------------
+__global__ void timestep_sincos_kernel(const int64_t* __restrict__ t, int R, const float* __restrict__ freqs,
+                                       float* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R * 128) return;
+  int r = i >> 7, k = i & 127;
+  // fit.py:73-76: freqs = exp(-ln(1e4) * arange(half) / half) in fp32 (computed on the HOST by the
+  // reference, so the caller may pass that exact table), args = t.float() * freqs
+  float f = freqs ? freqs[k] : expf(-9.210340371976184f * (float)k / 128.0f);
+  float a = (float)t[r] * f;
+  float s, c;
+  sincosf(a, &s, &c);
+  out[(size_t)r * 256 + k] = c;
+  out[(size_t)r * 256 + 128 + k] = s;
+}
+
+// --------------------------------------------------------------------------------------------
+// c = t_emb + table[y];  silu(c)
+// --------------------------------------------------------------------------------------------
+template <typename ActT>
+__global__ void cond_combine_kernel(const float* __restrict__ t_emb, int t_rows, const int64_t* __restrict__ y,
+                                    const float* __restrict__ table, int table_rows, int R, int D, float* __restrict__ c,
+                                    ActT* __restrict__ silu_c) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)R * D) return;
+  int r = (int)(i / D), j = (int)(i - (long)r * D);
+  long lbl = y[r];
+  lbl = lbl < 0 ? 0 : (lbl >= table_rows ? table_rows - 1 : lbl);
+  float v = t_emb[(size_t)(t_rows == 1 ? 0 : r) * D + j] + table[(size_t)lbl * D + j];
+  if (c) c[i] = v;
+  silu_c[i] = from_f32<ActT>(silu_acc(v));
+}
+
+// --------------------------------------------------------------------------------------------
+// LayerNorm + modulate: one warp per row, row cached in registers (D <= 2048, D % 8 == 0)
+// --------------------------------------------------------------------------------------------
+constexpr int LN_MAXV = 8;  // 8 vectors of 8 per lane
+
+template <typename InT, typename OutT>
+__global__ void __launch_bounds__(256) ln_modulate_kernel(const InT* __restrict__ x, int M, int D, int rows_per_sample,
+                                                          const float* __restrict__ shift, const float* __restrict__ scale,
+                                                          long ld_mod, OutT* __restrict__ out, float* __restrict__ mean_out,
+                                                          float* __restrict__ rstd_out) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const int nvec = D >> 3;
+  const InT* xr = x + (size_t)row * D;
+  Vec8<InT> v[LN_MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    int vi = lane + i * 32;
+    if (vi < nvec) {
+      v[i] = Vec8<InT>::load(xr + vi * 8);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s += v[i].v[e];
+    }
+  }
+  const float mu = warp_sum(s) / (float)D;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    int vi = lane + i * 32;
+    if (vi < nvec) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { float d = v[i].v[e] - mu; q = fmaf(d, d, q); }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)D + 1e-6f);
+  if (lane == 0) {
+    if (mean_out) mean_out[row] = mu;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+  const size_t mrow = (size_t)(row / rows_per_sample) * ld_mod;
+  OutT* orow = out + (size_t)row * D;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    int vi = lane + i * 32;
+    if (vi < nvec) {
+      Vec8<float> sh = Vec8<float>::load(shift + mrow + vi * 8);
+      Vec8<float> sc = Vec8<float>::load(scale + mrow + vi * 8);
+      Vec8<OutT> o;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o.v[e] = fmaf((v[i].v[e] - mu) * rstd, 1.0f + sc.v[e], sh.v[e]);
+      o.store(orow + vi * 8);
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// final layer: LN + modulate + Linear(D -> P) (+ unpatchify). One warp per token.
+// --------------------------------------------------------------------------------------------
+template <typename InT>
+__global__ void __launch_bounds__(256) final_layer_kernel(const InT* __restrict__ x, int R, int T, int D,
+                                                          const float* __restrict__ shift, const float* __restrict__ scale,
+                                                          long ld_mod, const float* __restrict__ w, const float* __restrict__ b,
+                                                          int P, float* __restrict__ out, int nchw, int C, int H, int W, int p) {
+  const long tok = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (tok >= (long)R * T) return;
+  const int r = (int)(tok / T), tk = (int)(tok - (long)r * T);
+  const int nvec = D >> 3;
+  const InT* xr = x + (size_t)tok * D;
+  Vec8<InT> v[LN_MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    int vi = lane + i * 32;
+    if (vi < nvec) {
+      v[i] = Vec8<InT>::load(xr + vi * 8);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s += v[i].v[e];
+    }
+  }
+  const float mu = warp_sum(s) / (float)D;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    int vi = lane + i * 32;
+    if (vi < nvec) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { float d = v[i].v[e] - mu; q = fmaf(d, d, q); }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)D + 1e-6f);
+  const size_t mrow = (size_t)r * ld_mod;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    int vi = lane + i * 32;
+    if (vi < nvec) {
+      Vec8<float> sh = Vec8<float>::load(shift + mrow + vi * 8);
+      Vec8<float> sc = Vec8<float>::load(scale + mrow + vi * 8);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[i].v[e] = fmaf((v[i].v[e] - mu) * rstd, 1.0f + sc.v[e], sh.v[e]);
+    }
+  }
+  const int nw = nchw ? (W / p) : 0;
+  for (int o = 0; o < P; ++o) {
+    const float* wr = w + (size_t)o * D;
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+      int vi = lane + i * 32;
+      if (vi < nvec) {
+        Vec8<float> wv = Vec8<float>::load(wr + vi * 8);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc = fmaf(v[i].v[e], wv.v[e], acc);
+      }
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      float val = acc + b[o];
+      if (nchw) {
+        int ih = tk / nw, iw = tk - ih * nw;
+        int c = o % C, pp = o / C;
+        int ph = pp / p, pw = pp - ph * p;
+        out[(((size_t)r * C + c) * H + (ih * p + ph)) * W + (iw * p + pw)] = val;
+      } else {
+        out[(size_t)tok * P + o] = val;
+      }
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// fused CFG combine + DDPM / DDIM step
+// --------------------------------------------------------------------------------------------
+template <bool DDIM>
+__global__ void __launch_bounds__(256) cfg_step_kernel(const float* __restrict__ x, const float* __restrict__ mo,
+                                                       const float* __restrict__ noise, float* __restrict__ sample,
+                                                       float* __restrict__ pred_xstart, int rows, long per_row,
+                                                       int cfg_pairs, float cfg_scale, float eta,
+                                                       const int64_t* __restrict__ t, const float* __restrict__ coef, int S) {
+  const long nvec = (long)rows * per_row / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    const long e0 = i * 4;
+    const int row = (int)(e0 / per_row);
+    const long off = e0 - (long)row * per_row;
+    long ti = t[row];
+    ti = ti < 0 ? 0 : (ti >= S ? S - 1 : ti);
+    const float* cf = coef + ti * 8;
+    const float c0 = cf[0], c1 = cf[1], c2 = cf[2], c3 = cf[3], logvar = cf[4];
+    const float4 xv = *reinterpret_cast<const float4*>(x + e0);
+    const float4 nv = *reinterpret_cast<const float4*>(noise + e0);
+    float4 ev;
+    if (cfg_pairs > 0) {
+      const int pair = row % cfg_pairs;
+      const float4 cv = *reinterpret_cast<const float4*>(mo + (size_t)pair * per_row + off);
+      const float4 uv = *reinterpret_cast<const float4*>(mo + (size_t)(pair + cfg_pairs) * per_row + off);
+      // fit.py:551: half_eps = uncond_eps + cfg_scale * (cond_eps - uncond_eps)
+      ev.x = uv.x + cfg_scale * (cv.x - uv.x); ev.y = uv.y + cfg_scale * (cv.y - uv.y);
+      ev.z = uv.z + cfg_scale * (cv.z - uv.z); ev.w = uv.w + cfg_scale * (cv.w - uv.w);
+    } else {
+      ev = *reinterpret_cast<const float4*>(mo + e0);
+    }
+    const float nz = (ti != 0) ? 1.f : 0.f;
+    float xs[4] = {xv.x, xv.y, xv.z, xv.w}, es[4] = {ev.x, ev.y, ev.z, ev.w}, ns[4] = {nv.x, nv.y, nv.z, nv.w};
+    float x0[4], out[4];
+    if (!DDIM) {
+      const float sig = nz * expf(0.5f * logvar);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        // no fma contraction across the reference's separate multiplies/adds: keep its rounding
+        x0[k] = __fsub_rn(__fmul_rn(c0, xs[k]), __fmul_rn(c1, es[k]));
+        float mean = __fadd_rn(__fmul_rn(c2, x0[k]), __fmul_rn(c3, xs[k]));
+        out[k] = __fadd_rn(mean, __fmul_rn(sig, ns[k]));
+      }
+    } else {
+      const float ab = cf[5], abp = cf[6];
+      const float sigma = eta * sqrtf((1.f - abp) / (1.f - ab)) * sqrtf(1.f - ab / abp);
+      const float sa = sqrtf(abp), sb = sqrtf(1.f - abp - sigma * sigma);
+      const float sn = nz * sigma;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        x0[k] = __fsub_rn(__fmul_rn(c0, xs[k]), __fmul_rn(c1, es[k]));
+        float e2 = __fdiv_rn(__fsub_rn(__fmul_rn(c0, xs[k]), x0[k]), c1);  // _predict_eps_from_xstart
+        float mean = __fadd_rn(__fmul_rn(x0[k], sa), __fmul_rn(sb, e2));
+        out[k] = __fadd_rn(mean, __fmul_rn(sn, ns[k]));
+      }
+    }
+    *reinterpret_cast<float4*>(sample + e0) = make_float4(out[0], out[1], out[2], out[3]);
+    if (pred_xstart) *reinterpret_cast<float4*>(pred_xstart + e0) = make_float4(x0[0], x0[1], x0[2], x0[3]);
+  }
+}
+
+__global__ void q_sample_kernel(const float* __restrict__ x0, const float* __restrict__ noise, float* __restrict__ out,
+                                int rows, long per_row, const int64_t* __restrict__ t, const float* __restrict__ a,
+                                const float* __restrict__ b, int S) {
+  const long nvec = (long)rows * per_row / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    const long e0 = i * 4;
+    const int row = (int)(e0 / per_row);
+    long ti = t[row];
+    ti = ti < 0 ? 0 : (ti >= S ? S - 1 : ti);
+    const float ca = a[ti], cb = b[ti];
+    const float4 xv = *reinterpret_cast<const float4*>(x0 + e0);
+    const float4 nv = *reinterpret_cast<const float4*>(noise + e0);
+    float4 o;
+    o.x = __fadd_rn(__fmul_rn(ca, xv.x), __fmul_rn(cb, nv.x));
+    o.y = __fadd_rn(__fmul_rn(ca, xv.y), __fmul_rn(cb, nv.y));
+    o.z = __fadd_rn(__fmul_rn(ca, xv.z), __fmul_rn(cb, nv.z));
+    o.w = __fadd_rn(__fmul_rn(ca, xv.w), __fmul_rn(cb, nv.w));
+    *reinterpret_cast<float4*>(out + e0) = o;
+  }
+}
+
+__global__ void gather_i64_kernel(const int64_t* __restrict__ map, int map_len, const int64_t* __restrict__ idx,
+                                  int64_t* __restrict__ out, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  long k = idx[i];
+  k = k < 0 ? 0 : (k >= map_len ? map_len - 1 : k);
+  out[i] = map[k];
+}
+__global__ void add_i64_kernel(int64_t* __restrict__ idx, int n, int64_t delta) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) idx[i] += delta;
+}
+
+}  // namespace fitb200
+
+using namespace fitb200;
+
+extern "C" {
+
+const char* fitb200_last_error(void) { return g_err; }
+int fitb200_version(void) { return 100; }
+
+int fitb200_device_ok(void) {
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+  return major == 10;
+}
+
+int fitb200_mask_to_kvlen(const uint8_t* mask, int R, int T, int32_t* kv_len, int32_t* n_valid, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(mask && kv_len && R > 0 && T > 0, "mask_to_kvlen: bad arguments");
+  mask_to_kvlen_kernel<<<ceil_div(R, 4), 128, 0, (cudaStream_t)stream>>>(mask, R, T, kv_len, n_valid);
+  FITB200_CHECK_LAUNCH("mask_to_kvlen");
+  return FITB200_OK;
+}
+
+int fitb200_embed_tokens_fwd(const float* x, int x_is_nchw, int R, int R_src, int C, int H, int W, int p, int T,
+                             const float* w, const float* b, int D, void* out, int out_dtype, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && w && b && out && R > 0 && R_src > 0 && T > 0 && D > 0 && p > 0 && C > 0, "embed_tokens: bad arguments");
+  const int K = p * p * C;
+  FITB200_CHECK_ARG(K % 4 == 0 && K <= 1024, "embed_tokens: p*p*C=%d must be a multiple of 4 and <= 1024", K);
+  if (x_is_nchw) FITB200_CHECK_ARG(H % p == 0 && W % p == 0 && (H / p) * (W / p) == T, "embed_tokens: T=%d != (H/p)*(W/p)", T);
+  dim3 grid((unsigned)ceil_div((long)R * T, (long)EMB_TOK), (unsigned)ceil_div(D, 128));
+  size_t smem = (size_t)EMB_TOK * K * sizeof(float);
+  FITB200_DISPATCH_ACT(out_dtype, OutT, {
+    if (smem > 48 * 1024) cudaFuncSetAttribute(embed_tokens_kernel<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    embed_tokens_kernel<OutT><<<grid, 128, smem, (cudaStream_t)stream>>>(x, x_is_nchw, R, R_src, C, H, W, p, T, w, b, D, (OutT*)out);
+  })
+  FITB200_CHECK_LAUNCH("embed_tokens");
+  return FITB200_OK;
+}
+
+int fitb200_timestep_sincos(const int64_t* t, int R, const float* freqs, float* out, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(t && out && R > 0, "timestep_sincos: bad arguments");
+  timestep_sincos_kernel<<<ceil_div(R * 128, 256), 256, 0, (cudaStream_t)stream>>>(t, R, freqs, out);
+  FITB200_CHECK_LAUNCH("timestep_sincos");
+  return FITB200_OK;
+}
+
+int fitb200_cond_combine_fwd(const float* t_emb, int t_rows, const int64_t* y, const float* table, int table_rows, int R,
+                             int D, float* c, void* silu_c, int act_dtype, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(t_emb && y && table && silu_c && R > 0 && D > 0 && (t_rows == 1 || t_rows == R), "cond_combine: bad arguments");
+  long n = (long)R * D;
+  FITB200_DISPATCH_ACT(act_dtype, ActT, {
+    cond_combine_kernel<ActT><<<(unsigned)ceil_div(n, 256L), 256, 0, (cudaStream_t)stream>>>(t_emb, t_rows, y, table, table_rows, R, D, c, (ActT*)silu_c);
+  })
+  FITB200_CHECK_LAUNCH("cond_combine");
+  return FITB200_OK;
+}
+
+int fitb200_ln_modulate_fwd(const void* x, int x_dtype, int M, int D, int rows_per_sample, const float* shift,
+                            const float* scale, int64_t ld_mod, void* out, int out_dtype, float* mean, float* rstd,
+                            fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && shift && scale && out && M > 0 && rows_per_sample > 0, "ln_modulate: bad arguments");
+  FITB200_CHECK_ARG(D % 8 == 0 && D <= 32 * 8 * LN_MAXV && ld_mod % 4 == 0, "ln_modulate: D=%d must be a multiple of 8 and <= %d", D, 32 * 8 * LN_MAXV);
+  dim3 grid((unsigned)ceil_div(M, 8));
+  FITB200_DISPATCH_ACT(x_dtype, InT, {
+    FITB200_DISPATCH_ACT(out_dtype, OutT, {
+      ln_modulate_kernel<InT, OutT><<<grid, 256, 0, (cudaStream_t)stream>>>((const InT*)x, M, D, rows_per_sample, shift, scale, ld_mod, (OutT*)out, mean, rstd);
+    })
+  })
+  FITB200_CHECK_LAUNCH("ln_modulate");
+  return FITB200_OK;
+}
+
+int fitb200_final_layer_fwd(const void* x, int x_dtype, int R, int T, int D, const float* shift, const float* scale,
+                            int64_t ld_mod, const float* w, const float* b, int P, float* out, int out_nchw, int C,
+                            int H, int W, int p, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && shift && scale && w && b && out && R > 0 && T > 0 && P > 0, "final_layer: bad arguments");
+  FITB200_CHECK_ARG(D % 8 == 0 && D <= 32 * 8 * LN_MAXV && ld_mod % 4 == 0, "final_layer: D=%d must be a multiple of 8 and <= %d", D, 32 * 8 * LN_MAXV);
+  if (out_nchw) FITB200_CHECK_ARG(p > 0 && C > 0 && P % C == 0 && P == p * p * C && H % p == 0 && W % p == 0 && (H / p) * (W / p) == T, "final_layer: inconsistent unpatchify shape");
+  dim3 grid((unsigned)ceil_div((long)R * T, 8L));
+  FITB200_DISPATCH_ACT(x_dtype, InT, {
+    final_layer_kernel<InT><<<grid, 256, 0, (cudaStream_t)stream>>>((const InT*)x, R, T, D, shift, scale, ld_mod, w, b, P, out, out_nchw, C, H, W, p);
+  })
+  FITB200_CHECK_LAUNCH("final_layer");
+  return FITB200_OK;
+}
+
+static int step_grid(long nvec) {
+  long want = ceil_div(nvec, 256L);
+  long cap = (long)sm_count() * 8;
+  return (int)(want < cap ? want : cap);
+}
+
+int fitb200_cfg_ddpm_step(const float* x, const float* model_out, const float* noise, float* sample, float* pred_xstart,
+                          int rows, int64_t per_row, int cfg_pairs, float cfg_scale, const int64_t* t, const float* coef,
+                          int S, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && model_out && noise && sample && t && coef && rows > 0 && per_row > 0 && S > 0, "ddpm_step: bad arguments");
+  FITB200_CHECK_ARG(per_row % 4 == 0, "ddpm_step: per-row element count %lld must be a multiple of 4", (long long)per_row);
+  FITB200_CHECK_ARG(cfg_pairs == 0 || rows == 2 * cfg_pairs, "ddpm_step: cfg_pairs must be 0 or rows/2");
+  long nvec = (long)rows * per_row / 4;
+  cfg_step_kernel<false><<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x, model_out, noise, sample, pred_xstart, rows, per_row, cfg_pairs, cfg_scale, 0.f, t, coef, S);
+  FITB200_CHECK_LAUNCH("ddpm_step");
+  return FITB200_OK;
+}
+
+int fitb200_cfg_ddim_step(const float* x, const float* model_out, const float* noise, float* sample, float* pred_xstart,
+                          int rows, int64_t per_row, int cfg_pairs, float cfg_scale, float eta, const int64_t* t,
+                          const float* coef, int S, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && model_out && noise && sample && t && coef && rows > 0 && per_row > 0 && S > 0, "ddim_step: bad arguments");
+  FITB200_CHECK_ARG(per_row % 4 == 0, "ddim_step: per-row element count %lld must be a multiple of 4", (long long)per_row);
+  FITB200_CHECK_ARG(cfg_pairs == 0 || rows == 2 * cfg_pairs, "ddim_step: cfg_pairs must be 0 or rows/2");
+  long nvec = (long)rows * per_row / 4;
+  cfg_step_kernel<true><<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x, model_out, noise, sample, pred_xstart, rows, per_row, cfg_pairs, cfg_scale, eta, t, coef, S);
+  FITB200_CHECK_LAUNCH("ddim_step");
+  return FITB200_OK;
+}
+
+int fitb200_q_sample(const float* x0, const float* noise, float* out, int rows, int64_t per_row, const int64_t* t,
+                     const float* sqrt_ac, const float* sqrt_1m_ac, int S, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x0 && noise && out && t && sqrt_ac && sqrt_1m_ac && rows > 0 && per_row > 0 && S > 0, "q_sample: bad arguments");
+  FITB200_CHECK_ARG(per_row % 4 == 0, "q_sample: per-row element count must be a multiple of 4");
+  long nvec = (long)rows * per_row / 4;
+  q_sample_kernel<<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x0, noise, out, rows, per_row, t, sqrt_ac, sqrt_1m_ac, S);
+  FITB200_CHECK_LAUNCH("q_sample");
+  return FITB200_OK;
+}
+
+int fitb200_gather_i64(const int64_t* map, int map_len, const int64_t* idx, int64_t* out, int n, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(map && idx && out && n > 0 && map_len > 0, "gather_i64: bad arguments");
+  gather_i64_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(map, map_len, idx, out, n);
+  FITB200_CHECK_LAUNCH("gather_i64");
+  return FITB200_OK;
+}
+
+int fitb200_add_i64(int64_t* idx, int n, int64_t delta, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(idx && n > 0, "add_i64: bad arguments");
+  add_i64_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(idx, n, delta);
+  FITB200_CHECK_LAUNCH("add_i64");
+  return FITB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+/* fit_b200 -- C ABI of the B200-native FiT denoising hot path (libfit_b200.so).
+ *
+ * The reference (jlnk03/FiT) has no FFI: its hot path sits behind the Python module interface
+ * `models.fit.FiT.forward / forward_with_cfg` (FiT/models/fit.py:474-553) and
+ * `diffusion.create_diffusion(...).p_sample / ddim_sample / q_sample`
+ * (FiT/diffusion/gaussian_diffusion.py:227-572).  fit_b200/models/fit.py and
+ * fit_b200/diffusion/ mirror those Python interfaces and call the entry points below through
+ * ctypes.  Each entry point cites the reference lines whose arithmetic it replaces.
+ *
+ * Conventions: plain pointers (device memory unless noted) + explicit sizes; the caller owns and
+ * allocates every buffer (no allocation, no synchronisation, no hidden state in the library, so
+ * every call is CUDA-graph capturable); all work is enqueued on `stream` (a cudaStream_t);
+ * return 0 on success or a negative FITB200_ERR_* code, message in fitb200_last_error().
+ * Row-major everywhere; "act dtype" is FITB200_F32 (verification mode) or FITB200_BF16.
+ */
+#ifndef FIT_B200_H
+#define FIT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* fitb200_stream_t; /* cudaStream_t */
+
+enum { FITB200_OK = 0, FITB200_ERR_INVALID_ARG = -1, FITB200_ERR_CUDA = -2, FITB200_ERR_UNSUPPORTED = -3 };
+enum { FITB200_F32 = 0, FITB200_BF16 = 1 };
+
+/* GEMM epilogues (all fused into the GEMM kernel) */
+enum {
+  FITB200_EPI_BIAS = 0,            /* out = acc + bias                      qkv (fit.py:234), adaLN (fit.py:323-324,329) */
+  FITB200_EPI_BIAS_SILU = 1,       /* out = silu(acc + bias)                t-embedder first Linear (fit.py:55-57) */
+  FITB200_EPI_BIAS_GATE_RESID = 2, /* out = resid + gate[sample] * (acc+bias)   proj / fc2 + adaLN-Zero gate + residual (fit.py:331-337) */
+  FITB200_EPI_SWIGLU = 3           /* out = silu(acc_g + b_g) * (acc_x + b_x)   SwiGLU fc1_g|fc1_x (fit.py:278-280) */
+};
+
+const char* fitb200_last_error(void);
+int fitb200_version(void);
+/* 1 if the current device is compute capability 10.x (tcgen05 / TMEM available). Host query only. */
+int fitb200_device_ok(void);
+
+/* ---- token mask -> per-sample key range ------------------------------------------------------
+ * kv_len[r] = 1 + index of the last True in mask[r, :] (0 if none); n_valid[r] = number of True.
+ * Replaces the mask broadcast of Attention.forward (fit.py:184-185) by a per-sample bound used
+ * for tile skipping; the mask bytes themselves are still honoured inside the attention kernel. */
+int fitb200_mask_to_kvlen(const uint8_t* mask, int R, int T, int32_t* kv_len, int32_t* n_valid, fitb200_stream_t stream);
+
+/* ---- patchify + x_embedder -------------------------------------------------------------------
+ * FiT.patchify (fit.py:466-472) fused with x_embedder Linear(p*p*C -> D) (fit.py:387-388,499-501).
+ * x: fp32; tokens [R_src, T, p*p*C] (x_is_nchw=0) or latents [R_src, C, H, W] (x_is_nchw=1,
+ * T must equal (H/p)*(W/p)).  Output row r reads source row r % R_src (forward_with_cfg's
+ * cat([half, half]), fit.py:545-546, without the copy).  w: [D, p*p*C] fp32, b: [D] fp32.
+ * out: [R, T, D] in out_dtype (the residual stream). */
+int fitb200_embed_tokens_fwd(const float* x, int x_is_nchw, int R, int R_src, int C, int H, int W, int p, int T,
+                             const float* w, const float* b, int D, void* out, int out_dtype,
+                             fitb200_stream_t stream);
+
+/* ---- timestep sinusoid -----------------------------------------------------------------------
+ * TimestepEmbedder.timestep_embedding (fit.py:61-80): out[r, :] = [cos(t f) | sin(t f)], dim 256.
+ * freqs: optional device fp32 [128] frequency table (the reference builds it on the host, fit.py:73-75;
+ * passing that table makes the arguments bit-identical); NULL = computed in-kernel. */
+int fitb200_timestep_sincos(const int64_t* t, int R, const float* freqs, float* out /* [R,256] */,
+                            fitb200_stream_t stream);
+
+/* ---- c = t_emb + y_emb, silu(c) ---------------------------------------------------------------
+ * LabelEmbedder gather (fit.py:114) + `c = t + y` (fit.py:505) + the SiLU that precedes every
+ * adaLN Linear (fit.py:323, dit.py:134).  t_emb has t_rows rows (1 = batch-uniform timestep, or R).
+ * Labels outside [0, table_rows) are clamped (the reference would raise).  c: fp32 [R,D] (nullable),
+ * silu_c: [R,D] in act dtype. */
+int fitb200_cond_combine_fwd(const float* t_emb, int t_rows, const int64_t* y, const float* table, int table_rows,
+                             int R, int D, float* c, void* silu_c, int act_dtype, fitb200_stream_t stream);
+
+/* ---- GEMM  out[M,N] = epilogue(A[M,K] . B[N,K]^T) --------------------------------------------- */
+typedef struct {
+  int32_t M, N, K;
+  const void* A; int64_t lda;      /* [M,K] activations */
+  const void* B; int64_t ldb;      /* [N,K] nn.Linear weight layout (fit.py:208,209,268,269,274,324) */
+  const void* B2;                  /* fp32 SWIGLU only: fc1_x weight [N,K] (B = fc1_g) */
+  const float* bias;               /* [N] or NULL */
+  const float* bias2;              /* fp32 SWIGLU only: fc1_x bias */
+  void* out; int64_t ldo; int32_t out_dtype;
+  int32_t epilogue;                /* FITB200_EPI_* */
+  const float* gate; int64_t ld_gate; int32_t rows_per_sample; /* GATE_RESID: gate[(m / rows_per_sample) * ld_gate + n] */
+  const void* resid; int64_t ld_resid; int32_t resid_dtype;    /* GATE_RESID: may alias out */
+} fitb200_gemm_args;
+
+/* fp32 FMA GEMM on CUDA cores: A, B, B2 fp32.  The fp32 verification mode and the small
+ * embedder GEMMs.  SWIGLU: N = hidden width, out [M,N]. */
+int fitb200_gemm_f32(const fitb200_gemm_args* a, fitb200_stream_t stream);
+
+/* bf16 tcgen05 GEMM: A, B bf16, fp32 accumulation in TMEM, operands staged by TMA.
+ * K % 8 == 0, N % 8 == 0, 16-byte aligned rows.  SWIGLU: B is the packed [N = 2*Hp, K] weight whose
+ * rows alternate 16 rows of fc1_g with the matching 16 rows of fc1_x (bias packed alike);
+ * out is [M, Hp]. */
+int fitb200_gemm_bf16_tc(const fitb200_gemm_args* a, fitb200_stream_t stream);
+
+/* ---- LayerNorm(eps 1e-6, no affine) + adaLN modulate -------------------------------------------
+ * modulate(norm(x), shift, scale) (fit.py:45-46,303,308,332,336): out = LN(x) * (1 + scale[s]) + shift[s],
+ * s = row / rows_per_sample.  shift/scale: fp32 with row stride ld_mod.  mean/rstd: optional fp32 [M]
+ * (saved for backward). */
+int fitb200_ln_modulate_fwd(const void* x, int x_dtype, int M, int D, int rows_per_sample, const float* shift,
+                            const float* scale, int64_t ld_mod, void* out, int out_dtype, float* mean, float* rstd,
+                            fitb200_stream_t stream);
+
+/* ---- fused attention: 2-D RoPE on q,k + key-masked softmax(q k^T / sqrt(d)) v -------------------
+ * apply_rotary_emb (fit.py:160-174) + Attention.forward (fit.py:176-188) + _rearange_out (fit.py:220-227).
+ * qkv: [R, T, 3, h, d] (the qkv Linear output, column = which*h*d + head*d + i, fit.py:234-235).
+ * freqs: fp32 [freqs_rows, T, d] interleaved (cos, sin) pairs (freqs_rows = 1 broadcasts, fit.py:166-167).
+ * Key j of sample r takes part iff j < kv_len[r] and (mask == NULL or mask[r*T + j]).
+ * Query tiles starting at or beyond kv_len[r] are skipped and their output rows zero-filled (they are
+ * padding whose reference output is unspecified).  out: [R, T, h*d].
+ * lse: optional fp32 [R, h, T] log-sum-exp (natural log, of the scaled scores) for backward.
+ * d in {64, 72}. */
+int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, int freqs_rows, const int32_t* kv_len,
+                     const uint8_t* mask, int R, int T, int h, int d, void* out, float* lse,
+                     fitb200_stream_t stream);
+
+/* ---- final layer ---------------------------------------------------------------------------------
+ * FinalLayer.forward (dit.py:138-142) after its adaLN Linear: LN + modulate + Linear(D -> P) with
+ * P = p*p*C_out, optionally fused with FiT.unpatchify (fit.py:444-456).
+ * out: fp32 tokens [R, T, P] (out_nchw = 0) or latents [R, C, H, W] (out_nchw = 1, T = (H/p)*(W/p)). */
+int fitb200_final_layer_fwd(const void* x, int x_dtype, int R, int T, int D, const float* shift, const float* scale,
+                            int64_t ld_mod, const float* w, const float* b, int P, float* out, int out_nchw, int C,
+                            int H, int W, int p, fitb200_stream_t stream);
+
+/* ---- diffusion step ------------------------------------------------------------------------------
+ * coef: device fp32 table [S, 8] per (respaced) timestep:
+ *   0 sqrt_recip_alphas_cumprod   1 sqrt_recipm1_alphas_cumprod   2 posterior_mean_coef1
+ *   3 posterior_mean_coef2        4 model log-variance (FIXED_LARGE / FIXED_SMALL)
+ *   5 alphas_cumprod              6 alphas_cumprod_prev           7 (unused)
+ * (gaussian_diffusion.py:179-213,307-320), each the float64 table value cast to fp32 exactly as
+ * _extract_into_tensor does (:891).
+ * cfg_pairs = B > 0: model_out holds the raw network output for rows [0,B) conditional and [B,2B)
+ * unconditional and the classifier-free-guidance combine of forward_with_cfg (fit.py:549-552) is
+ * applied on the fly: eps[r] = u + s (c - u) with pair index r % B.  cfg_pairs = 0: model_out is eps.
+ * ddpm: p_mean_variance EPSILON branch, clip_denoised=False (:332-335,346-351,244-264) + p_sample (:422-428):
+ *   x0 = c0 x - c1 eps;  mean = c2 x0 + c3 x;  sample = mean + (t != 0) exp(0.5 logvar) noise.
+ * ddim (:553-572): eps' re-derived from x0, sigma = eta sqrt((1-ab_prev)/(1-ab)) sqrt(1-ab/ab_prev),
+ *   sample = sqrt(ab_prev) x0 + sqrt(1-ab_prev-sigma^2) eps' + (t != 0) sigma noise.
+ * t: device int64 [rows] indices into coef.  pred_xstart nullable.  sample may alias x. */
+int fitb200_cfg_ddpm_step(const float* x, const float* model_out, const float* noise, float* sample,
+                          float* pred_xstart, int rows, int64_t per_row, int cfg_pairs, float cfg_scale,
+                          const int64_t* t, const float* coef, int S, fitb200_stream_t stream);
+int fitb200_cfg_ddim_step(const float* x, const float* model_out, const float* noise, float* sample,
+                          float* pred_xstart, int rows, int64_t per_row, int cfg_pairs, float cfg_scale, float eta,
+                          const int64_t* t, const float* coef, int S, fitb200_stream_t stream);
+
+/* q_sample (gaussian_diffusion.py:227-242) = DDIMScheduler.add_noise call site (FiT/train.py:53):
+ * out = a[t] x0 + b[t] noise with a = sqrt_alphas_cumprod, b = sqrt_one_minus_alphas_cumprod (fp32 [S]). */
+int fitb200_q_sample(const float* x0, const float* noise, float* out, int rows, int64_t per_row, const int64_t* t,
+                     const float* sqrt_ac, const float* sqrt_1m_ac, int S, fitb200_stream_t stream);
+
+/* loop plumbing for CUDA-graph replay of the sampling loop (gaussian_diffusion.py:679, respace.py:125-126):
+ * out[i] = map[clamp(idx[i])]; and idx[i] += delta. */
+int fitb200_gather_i64(const int64_t* map, int map_len, const int64_t* idx, int64_t* out, int n, fitb200_stream_t stream);
+int fitb200_add_i64(int64_t* idx, int n, int64_t delta, fitb200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FIT_B200_H */
