@@ -1,0 +1,331 @@
+#!/usr/bin/env python
+"""Headline benchmark: FiT-XL/2 256x256 sampling images/sec (250-step DDPM, CFG 1.5, batch 256 per GPU).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # fit_b200 (CUDA) arm
+    python bench.py --impl reference [--steps K] [--warmup W]      # the reference algorithm on the host CPU cores
+
+A "step" is ONE denoising step of the whole batch: FiT-XL/2 forward on 2 x batch rows (conditional | null class)
++ the fused CFG + p_sample update.  images/sec = batch / (250 x seconds per step).  With N GPUs every rank samples its
+own `--batch` images (weak scaling, no collective on the data path); value = N x batch / (250 x max-over-ranks step time).
+One JSON line on stdout (rank 0).  Nothing here reads /root/reference.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+STEPS_PER_IMAGE = 250
+METRIC = "FiT-XL/2 sampling images/sec @256^2 (250-step DDPM, CFG 1.5)"
+
+
+# ------------------------------------------------------------------------------------------------ FLOP model
+def forward_flops(D, Hd, L, T, p2c=16):
+    """Algorithmic FLOPs of one sample forward with T valid tokens (2 per MAC), SURVEY.md section 8(d)."""
+    return L * (T * (8 * D * D + 6 * D * Hd) + 4 * T * T * D + 12 * D * D) + 2 * T * p2c * D + 2 * (256 * D + D * D) + 4 * D * D + 2 * T * D * p2c
+
+
+MODELS = {"FiT-XL/2": (1152, 3072, 28, 16), "FiT-B/2": (768, 2048, 12, 12), "FiT-S/2": (384, 1024, 12, 6)}
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            pk = json.load(fh)
+        return {"hbm_gbs": pk["hbm_gbs"], "tf_burst": pk["bf16_tflops"], "tf_sustained": pk.get("bf16_tflops_sustained", pk["bf16_tflops"]),
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+# ------------------------------------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 6:
+                continue
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except ValueError:
+                continue
+            for nme, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm (oracle port)
+def cpu_reference_run(model_name: str, images: int, steps: int, warmup: int):
+    """The reference algorithm (oracle restatement of fit.py / gaussian_diffusion.py, pinned to the reference's goldens) on
+    the host cores: `images` latents (2 x images rows with CFG), `steps` timed denoising steps.  Returns (img/s, s/step, info)."""
+    import torch
+    from oracle import diffusion_oracle as do
+    from oracle import fit_oracle as fo
+    from oracle.pos_embed_oracle import precompute_freqs_cis_2d
+    torch.set_num_threads(os.cpu_count() or 1)
+    cfg = fo.model_config(model_name)
+    sd = fo.random_state_dict(cfg, seed=0)
+    d = cfg["hidden_size"] // cfg["num_heads"]
+    tb, tmap = do.create(str(STEPS_PER_IMAGE))
+    g = torch.Generator().manual_seed(123)
+    z = torch.randn(images, 4, 32, 32, generator=g)
+    x = torch.cat([z, z], 0)
+    y = torch.cat([torch.randint(0, 1000, (images,), generator=g), torch.full((images,), 1000)])
+    pos = torch.tensor(precompute_freqs_cis_2d(d, 16, 16, max_length=256), dtype=torch.float32)[None]
+    mask = torch.ones(2 * images, 256, dtype=torch.bool)
+    tmap_t = torch.tensor(tmap)
+    times = []
+    with torch.no_grad():
+        for k in range(warmup + steps):
+            i = STEPS_PER_IMAGE - 1 - k
+            t0 = time.perf_counter()
+            t = torch.full((2 * images,), i, dtype=torch.long)
+            eps = fo.forward_with_cfg(sd, cfg, x, tmap_t[t], y, pos, mask, 1.5)
+            x = do.p_sample(tb, x, t, eps, torch.randn(x.shape, generator=g))["sample"]
+            if k >= warmup:
+                times.append(time.perf_counter() - t0)
+    s_step = sum(times) / len(times)
+    return images / (STEPS_PER_IMAGE * s_step), s_step, {"cores": torch.get_num_threads(), "images": images, "steps": steps}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 4))
+    warm = 1 if args.warmup > 0 else 0
+    val, s_step, info = cpu_reference_run(args.model, images=2, steps=steps, warmup=warm)
+    sample = (f"{info['images']} images ({2 * info['images']} rows with CFG) x {steps} of the 250 denoising steps, fp32, "
+              f"{info['cores']} threads; img/s = images / (250 x s/step)")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "images/sec", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
+            "ms_per_step": s_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.model} 256x256 (32x32x4 latent, 256 tokens), 250-step DDPM p_sample, CFG 1.5; CPU sample of the same step",
+                       "steps_per_image": STEPS_PER_IMAGE},
+            "cpu_baseline": {"value": val, "unit": "images/sec", "cores": info["cores"], "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ CUDA arm
+def randomize_zero_init(model, seed=1):
+    """adaLN-Zero zero-initialises the modulation and output layers (fit.py:421-430): the random-init network would be the
+    identity and output 0.  Re-draw those parameters N(0, 0.02) so the benchmark computes on non-degenerate values."""
+    import torch
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    for name, p in model.named_parameters():
+        if "adaLN_modulation" in name or name.startswith("final_layer.linear") or name.endswith(".bias"):
+            p.data.copy_(torch.randn(p.shape, generator=g) * 0.02)
+
+
+def time_kernel(fn, iters, flush):
+    import torch
+    fn(); fn()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(iters):
+        flush()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+    return tot / iters * 1e-3
+
+
+def kernel_rooflines(model, sampler, peaks, iters=5):
+    """Per-kernel roofline, timed alone with CUDA events on the launch stream (L2 flushed between iterations)."""
+    import torch
+    from fit_b200 import ops
+    from fit_b200._lib import EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_SWIGLU
+    eng = model.engine
+    W = eng.weights()
+    ws = eng.workspace(2 * sampler.B, sampler.T, sampler.device)
+    e = W.blocks[0]
+    D, T, M = model.hidden_size, sampler.T, ws.xs.shape[0]
+    Hp = W.Hp
+    h, dh = model.num_heads, model.hidden_size // model.num_heads
+    sh1, sc1, g1, sh2, sc2, g2 = ws.mod_views[0]
+    scratch = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=sampler.device)  # 256 MB > 126 MB L2
+    flush = lambda: scratch.fill_(1.0)  # noqa: E731
+    bpe = ws.xs.element_size()
+    res = {}
+
+    def add(name, fn, flops, bytes_):
+        t = time_kernel(fn, iters, flush)
+        tf, gbs = flops / t / 1e12, bytes_ / t / 1e9
+        tensor_bound = flops / (peaks["tf_burst"] * 1e12) >= bytes_ / (peaks["hbm_gbs"] * 1e9)
+        res[name] = {"bound": "tensor" if tensor_bound else "hbm", "ms": t * 1e3,
+                     "achieved": tf if tensor_bound else gbs, "peak": peaks["tf_burst"] if tensor_bound else peaks["hbm_gbs"],
+                     "unit": "TFLOP/s" if tensor_bound else "GB/s",
+                     "frac": (tf / peaks["tf_burst"]) if tensor_bound else (gbs / peaks["hbm_gbs"]), "traffic": None}
+
+    add("gemm_tc[swiglu fc1_g|fc1_x]", lambda: ops.gemm(ws.h, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU),
+        2.0 * M * D * 2 * Hp, (M * D + 2 * Hp * D + M * Hp) * 2)
+    add("gemm_tc[qkv]", lambda: ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS), 2.0 * M * D * 3 * D, (M * D + 3 * D * D + M * 3 * D) * 2)
+    add("gemm_tc[fc2+gate+resid]", lambda: ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=W.n_mod,
+                                                     rows_per_sample=T, resid=ws.xs), 2.0 * M * Hp * D, (M * Hp + D * Hp) * 2 + 2 * M * D * bpe)
+    add("gemm_tc[proj+gate+resid]", lambda: ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=W.n_mod,
+                                                      rows_per_sample=T, resid=ws.xs), 2.0 * M * D * D, (M * D + D * D) * 2 + 2 * M * D * bpe)
+    add("attn_fwd[rope+softmax]", lambda: ops.attention(ws.qkv, sampler.pos, ws.kv_len, sampler.mask, 2 * sampler.B, T, h, dh, ws.att),
+        4.0 * (2 * sampler.B) * T * T * D, (M * 3 * D + M * D) * 2)
+    add("ln_modulate", lambda: ops.ln_modulate(ws.xs, sh1, sc1, W.n_mod, T, ws.h), 0.0, M * D * (bpe + 2))
+    tb = sampler.diffusion._tables(sampler.device)
+    nel = sampler.x.numel()
+    add("cfg_ddpm_step", lambda: ops.cfg_step(sampler.x, sampler.raw, sampler.noise, sampler.t_idx[: sampler.B], tb["coef"], cfg_pairs=sampler.B,
+                                              cfg_scale=1.5, sample=sampler.x), 0.0, nel * 4 * 5)
+    return res
+
+
+def run_cuda_arm(args):
+    import torch
+    import torch.distributed as dist
+    from fit_b200.diffusion import create_diffusion
+    from fit_b200.models.fit import FiT_models
+    from fit_b200.sampler import CFGSampler
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py: no CUDA device; fit_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    peaks = load_peaks()
+    D, Hd, L, heads = MODELS[args.model]
+    B = args.batch
+    torch.manual_seed(0)
+    with torch.device(dev):
+        model = FiT_models[args.model](precision=args.precision)
+    randomize_zero_init(model)
+    model = model.eval()
+    diffusion = create_diffusion(str(STEPS_PER_IMAGE))
+    dh = D // heads
+    from fit_b200.rope import precompute_freqs_cis_2d
+    pos = torch.tensor(precompute_freqs_cis_2d(dh, 16, 16, max_length=256), dtype=torch.float32)[None]
+    g = torch.Generator().manual_seed(1000 + rank)
+    z_host = torch.randn(B, 4, 32, 32, generator=g).pin_memory()
+    y_host = torch.randint(0, 1000, (B,), generator=g).pin_memory()
+    out_host = torch.empty(B, 4, 32, 32).pin_memory()
+    sampler = CFGSampler(model, diffusion, batch=B, latent_hw=(32, 32), cfg_scale=1.5, seed=1234, row_offset=rank * B)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident inputs, K graph-replayed steps, CUDA events, max over ranks
+    sampler.load(z_host, y_host, pos)
+    sampler.run(args.warmup if args.warmup > 0 else 1)
+    clocks = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    sampler.run(args.steps)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop() if rank == 0 else None
+    # ---- e2e: the user-level call with HOST buffers: H2D of latents + labels + RoPE table, K steps, D2H of the result
+    barrier()
+    t0 = time.perf_counter()
+    sampler.load(z_host, y_host, pos)
+    sampler.run(args.steps)
+    out_host.copy_(sampler.x, non_blocking=True)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    tms = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(tms[0]), float(tms[1])
+    assert bool(torch.isfinite(out_host).all()), "non-finite latents"
+    if rank == 0:
+        ms_step = ms / args.steps
+        value = world * B / (STEPS_PER_IMAGE * ms_step * 1e-3)
+        e2e_val = world * B / (STEPS_PER_IMAGE * (e2e_ms / args.steps) * 1e-3)
+        flops_img = 2 * STEPS_PER_IMAGE * forward_flops(D, Hd, L, 256)
+        kr = kernel_rooflines(model, sampler, peaks)
+        dom = kr["gemm_tc[swiglu fc1_g|fc1_x]"]
+        roof = dict(dom, kernel="gemm_tc_kernel<256, SWIGLU> (fc1_g|fc1_x, M=%d K=%d N=%d)" % (2 * B * 256, D, 2 * Hd), peak_source=peaks["source"],
+                    whole_step_tflops=value / world * flops_img / 1e12, whole_step_frac_of_sustained=value / world * flops_img / 1e12 / peaks["tf_sustained"],
+                    kernels=kr)
+        cpu = None
+        if not args.no_cpu_baseline:
+            cv, cs, info = cpu_reference_run(args.model, images=1, steps=2, warmup=1)
+            cpu = {"value": cv, "unit": "images/sec", "cores": info["cores"], "kind": "port",
+                   "sample": f"1 image (2 rows with CFG) x 2 of the 250 denoising steps of the same {args.model} workload, fp32 oracle port, "
+                             f"{cs:.2f} s/step; img/s = 1 / (250 x s/step)"}
+        line = {"metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+                "config": {"workload": f"{args.model} 256x256 (32x32x4 latent, 256 tokens), 250-step DDPM p_sample, CFG 1.5, batch {B} per GPU "
+                                       f"({2 * B} rows per step), random-init weights (adaLN-Zero params re-drawn N(0,0.02))",
+                           "steps_per_image": STEPS_PER_IMAGE, "per_gpu_batch": B, "global_batch": world * B, "parallelism": f"batch-sharded x{world}, no collective",
+                           "l2": "activations per step (>300 MB per tensor) exceed the 126 MB L2; per-kernel timings flush L2 with a 256 MB write",
+                           "step_definition": "one denoising step of the whole batch; images/sec = global_batch / (250 x s/step)"},
+                "clocks": clk, "gpu_launches": args.steps * sampler.kernels_per_step(),
+                "e2e": {"value": e2e_val, "unit": "images/sec", "h2d_bytes_per_step": (z_host.numel() * 4 + y_host.numel() * 8 + pos.numel() * 4) / args.steps,
+                        "d2h_bytes_per_step": out_host.numel() * 4 / args.steps,
+                        "note": "CFGSampler.load (pinned host latents/labels/RoPE table -> device) + K graph-replayed steps + device -> pinned host copy of the latents"},
+                "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="fit_b200", choices=["fit_b200", "reference"])
+    ap.add_argument("--model", default="FiT-XL/2", choices=sorted(MODELS))
+    ap.add_argument("--batch", type=int, default=256, help="images per GPU")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_cuda_arm(args)
+
+
+if __name__ == "__main__":
+    main()

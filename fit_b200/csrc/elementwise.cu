@@ -269,10 +269,12 @@ __global__ void __launch_bounds__(256) final_layer_kernel(const InT* __restrict_
 template <bool DDIM>
 __global__ void __launch_bounds__(256) cfg_step_kernel(const float* __restrict__ x, const float* __restrict__ mo,
                                                        const float* __restrict__ noise, float* __restrict__ sample,
-                                                       float* __restrict__ pred_xstart, int rows, long per_row,
-                                                       int cfg_pairs, float cfg_scale, float eta,
-                                                       const int64_t* __restrict__ t, const float* __restrict__ coef, int S) {
+                                                       float* __restrict__ pred_xstart, float* __restrict__ mean_out,
+                                                       int rows, long per_row, int cfg_pairs, float cfg_scale, float eta,
+                                                       int flags, const int64_t* __restrict__ t,
+                                                       const float* __restrict__ coef, int S) {
   const long nvec = (long)rows * per_row / 4;
+  const bool clip = flags & FITB200_STEP_CLIP_DENOISED, start_x = flags & FITB200_STEP_PREDICT_XSTART;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
     const long e0 = i * 4;
     const int row = (int)(e0 / per_row);
@@ -282,30 +284,36 @@ __global__ void __launch_bounds__(256) cfg_step_kernel(const float* __restrict__
     const float* cf = coef + ti * 8;
     const float c0 = cf[0], c1 = cf[1], c2 = cf[2], c3 = cf[3], logvar = cf[4];
     const float4 xv = *reinterpret_cast<const float4*>(x + e0);
-    const float4 nv = *reinterpret_cast<const float4*>(noise + e0);
+    float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (noise) nv = *reinterpret_cast<const float4*>(noise + e0);
     float4 ev;
     if (cfg_pairs > 0) {
       const int pair = row % cfg_pairs;
       const float4 cv = *reinterpret_cast<const float4*>(mo + (size_t)pair * per_row + off);
       const float4 uv = *reinterpret_cast<const float4*>(mo + (size_t)(pair + cfg_pairs) * per_row + off);
       // fit.py:551: half_eps = uncond_eps + cfg_scale * (cond_eps - uncond_eps)
-      ev.x = uv.x + cfg_scale * (cv.x - uv.x); ev.y = uv.y + cfg_scale * (cv.y - uv.y);
-      ev.z = uv.z + cfg_scale * (cv.z - uv.z); ev.w = uv.w + cfg_scale * (cv.w - uv.w);
+      ev.x = __fadd_rn(uv.x, __fmul_rn(cfg_scale, __fsub_rn(cv.x, uv.x)));
+      ev.y = __fadd_rn(uv.y, __fmul_rn(cfg_scale, __fsub_rn(cv.y, uv.y)));
+      ev.z = __fadd_rn(uv.z, __fmul_rn(cfg_scale, __fsub_rn(cv.z, uv.z)));
+      ev.w = __fadd_rn(uv.w, __fmul_rn(cfg_scale, __fsub_rn(cv.w, uv.w)));
     } else {
       ev = *reinterpret_cast<const float4*>(mo + e0);
     }
     const float nz = (ti != 0) ? 1.f : 0.f;
     float xs[4] = {xv.x, xv.y, xv.z, xv.w}, es[4] = {ev.x, ev.y, ev.z, ev.w}, ns[4] = {nv.x, nv.y, nv.z, nv.w};
-    float x0[4], out[4];
+    float x0[4], out[4], mean[4];
+    // no fma contraction across the reference's separate multiplies/adds: keep its rounding
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      // _predict_xstart_from_eps (gaussian_diffusion.py:346-351) or the START_X branch (:328-331)
+      x0[k] = start_x ? es[k] : __fsub_rn(__fmul_rn(c0, xs[k]), __fmul_rn(c1, es[k]));
+      if (clip) x0[k] = fminf(fmaxf(x0[k], -1.f), 1.f);  // process_xstart (:322-326)
+      mean[k] = __fadd_rn(__fmul_rn(c2, x0[k]), __fmul_rn(c3, xs[k]));  // q_posterior_mean_variance (:253-256)
+    }
     if (!DDIM) {
       const float sig = nz * expf(0.5f * logvar);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        // no fma contraction across the reference's separate multiplies/adds: keep its rounding
-        x0[k] = __fsub_rn(__fmul_rn(c0, xs[k]), __fmul_rn(c1, es[k]));
-        float mean = __fadd_rn(__fmul_rn(c2, x0[k]), __fmul_rn(c3, xs[k]));
-        out[k] = __fadd_rn(mean, __fmul_rn(sig, ns[k]));
-      }
+      for (int k = 0; k < 4; ++k) out[k] = __fadd_rn(mean[k], __fmul_rn(sig, ns[k]));
     } else {
       const float ab = cf[5], abp = cf[6];
       const float sigma = eta * sqrtf((1.f - abp) / (1.f - ab)) * sqrtf(1.f - ab / abp);
@@ -313,14 +321,32 @@ __global__ void __launch_bounds__(256) cfg_step_kernel(const float* __restrict__
       const float sn = nz * sigma;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        x0[k] = __fsub_rn(__fmul_rn(c0, xs[k]), __fmul_rn(c1, es[k]));
-        float e2 = __fdiv_rn(__fsub_rn(__fmul_rn(c0, xs[k]), x0[k]), c1);  // _predict_eps_from_xstart
-        float mean = __fadd_rn(__fmul_rn(x0[k], sa), __fmul_rn(sb, e2));
-        out[k] = __fadd_rn(mean, __fmul_rn(sn, ns[k]));
+        float e2 = __fdiv_rn(__fsub_rn(__fmul_rn(c0, xs[k]), x0[k]), c1);  // _predict_eps_from_xstart (:353-356)
+        float mp = __fadd_rn(__fmul_rn(x0[k], sa), __fmul_rn(sb, e2));
+        out[k] = __fadd_rn(mp, __fmul_rn(sn, ns[k]));
       }
     }
-    *reinterpret_cast<float4*>(sample + e0) = make_float4(out[0], out[1], out[2], out[3]);
+    if (sample) *reinterpret_cast<float4*>(sample + e0) = make_float4(out[0], out[1], out[2], out[3]);
     if (pred_xstart) *reinterpret_cast<float4*>(pred_xstart + e0) = make_float4(x0[0], x0[1], x0[2], x0[3]);
+    if (mean_out) *reinterpret_cast<float4*>(mean_out + e0) = make_float4(mean[0], mean[1], mean[2], mean[3]);
+  }
+}
+
+// forward_with_cfg's combine alone (fit.py:549-553): out[r] = u + s (c - u) for both halves
+__global__ void __launch_bounds__(256) cfg_combine_kernel(const float* __restrict__ mo, float* __restrict__ out, int pairs,
+                                                          long per_row, float s) {
+  const long nvec = (long)pairs * per_row / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    const long e0 = i * 4;
+    const float4 cv = *reinterpret_cast<const float4*>(mo + e0);
+    const float4 uv = *reinterpret_cast<const float4*>(mo + (size_t)pairs * per_row + e0);
+    float4 o;
+    o.x = __fadd_rn(uv.x, __fmul_rn(s, __fsub_rn(cv.x, uv.x)));
+    o.y = __fadd_rn(uv.y, __fmul_rn(s, __fsub_rn(cv.y, uv.y)));
+    o.z = __fadd_rn(uv.z, __fmul_rn(s, __fsub_rn(cv.z, uv.z)));
+    o.w = __fadd_rn(uv.w, __fmul_rn(s, __fsub_rn(cv.w, uv.w)));
+    *reinterpret_cast<float4*>(out + e0) = o;
+    *reinterpret_cast<float4*>(out + (size_t)pairs * per_row + e0) = o;
   }
 }
 
@@ -342,6 +368,48 @@ __global__ void q_sample_kernel(const float* __restrict__ x0, const float* __res
     o.z = __fadd_rn(__fmul_rn(ca, xv.z), __fmul_rn(cb, nv.z));
     o.w = __fadd_rn(__fmul_rn(ca, xv.w), __fmul_rn(cb, nv.w));
     *reinterpret_cast<float4*>(out + e0) = o;
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// counter-based N(0,1) noise: Philox4x32-10 keyed by (seed, step), counter = global element index / 4,
+// Box-Muller.  Keyed by the GLOBAL row index so a batch sharded over GPUs draws the same noise per image.
+// --------------------------------------------------------------------------------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+    const uint32_t n0 = hi1 ^ c[1] ^ k0, n1 = lo1, n2 = hi0 ^ c[3] ^ k1, n3 = lo0;
+    c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+}
+
+__global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ out, int rows, long per_row, uint64_t seed,
+                                                            const int64_t* __restrict__ step_ptr, long row_offset) {
+  const long nvec = (long)rows * per_row / 4;
+  const uint64_t step = (uint64_t)(step_ptr ? step_ptr[0] : 0);
+  const uint32_t k0 = (uint32_t)seed ^ (uint32_t)(step * 0x9E3779B97F4A7C15ull >> 32);
+  const uint32_t k1 = (uint32_t)(seed >> 32) ^ (uint32_t)step;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    const uint64_t gi = (uint64_t)(row_offset * (per_row / 4) + i);
+    uint32_t c[4] = {(uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)step, 0x46495442u /* "FITB" */};
+    philox4x32_10(c, k0, k1);
+    float4 o;
+    {
+      const float u1 = ((float)c[0] + 0.5f) * 2.3283064365386963e-10f, u2 = ((float)c[1] + 0.5f) * 2.3283064365386963e-10f;
+      const float r = sqrtf(-2.0f * logf(fminf(u1, 0.99999994f))), a = 6.283185307179586f * u2;
+      float sn, cs; sincosf(a, &sn, &cs);
+      o.x = r * cs; o.y = r * sn;
+    }
+    {
+      const float u1 = ((float)c[2] + 0.5f) * 2.3283064365386963e-10f, u2 = ((float)c[3] + 0.5f) * 2.3283064365386963e-10f;
+      const float r = sqrtf(-2.0f * logf(fminf(u1, 0.99999994f))), a = 6.283185307179586f * u2;
+      float sn, cs; sincosf(a, &sn, &cs);
+      o.z = r * cs; o.w = r * sn;
+    }
+    *reinterpret_cast<float4*>(out + i * 4) = o;
   }
 }
 
@@ -450,27 +518,40 @@ static int step_grid(long nvec) {
   return (int)(want < cap ? want : cap);
 }
 
-int fitb200_cfg_ddpm_step(const float* x, const float* model_out, const float* noise, float* sample, float* pred_xstart,
-                          int rows, int64_t per_row, int cfg_pairs, float cfg_scale, const int64_t* t, const float* coef,
-                          int S, fitb200_stream_t stream) {
-  FITB200_CHECK_ARG(x && model_out && noise && sample && t && coef && rows > 0 && per_row > 0 && S > 0, "ddpm_step: bad arguments");
-  FITB200_CHECK_ARG(per_row % 4 == 0, "ddpm_step: per-row element count %lld must be a multiple of 4", (long long)per_row);
-  FITB200_CHECK_ARG(cfg_pairs == 0 || rows == 2 * cfg_pairs, "ddpm_step: cfg_pairs must be 0 or rows/2");
+static int launch_step(bool ddim, const float* x, const float* model_out, const float* noise, float* sample,
+                       float* pred_xstart, float* mean, int rows, int64_t per_row, int cfg_pairs, float cfg_scale,
+                       float eta, int flags, const int64_t* t, const float* coef, int S, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && model_out && t && coef && rows > 0 && per_row > 0 && S > 0, "diffusion step: bad arguments");
+  FITB200_CHECK_ARG(sample || pred_xstart || mean, "diffusion step: no output requested");
+  FITB200_CHECK_ARG(per_row % 4 == 0, "diffusion step: per-row element count %lld must be a multiple of 4", (long long)per_row);
+  FITB200_CHECK_ARG(cfg_pairs == 0 || rows == 2 * cfg_pairs || rows == cfg_pairs, "diffusion step: cfg_pairs must be 0, rows or rows/2");
   long nvec = (long)rows * per_row / 4;
-  cfg_step_kernel<false><<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x, model_out, noise, sample, pred_xstart, rows, per_row, cfg_pairs, cfg_scale, 0.f, t, coef, S);
-  FITB200_CHECK_LAUNCH("ddpm_step");
+  if (ddim)
+    cfg_step_kernel<true><<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x, model_out, noise, sample, pred_xstart, mean, rows, per_row, cfg_pairs, cfg_scale, eta, flags, t, coef, S);
+  else
+    cfg_step_kernel<false><<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x, model_out, noise, sample, pred_xstart, mean, rows, per_row, cfg_pairs, cfg_scale, 0.f, flags, t, coef, S);
+  FITB200_CHECK_LAUNCH("diffusion step");
   return FITB200_OK;
 }
 
+int fitb200_cfg_ddpm_step(const float* x, const float* model_out, const float* noise, float* sample, float* pred_xstart,
+                          float* mean, int rows, int64_t per_row, int cfg_pairs, float cfg_scale, int flags,
+                          const int64_t* t, const float* coef, int S, fitb200_stream_t stream) {
+  return launch_step(false, x, model_out, noise, sample, pred_xstart, mean, rows, per_row, cfg_pairs, cfg_scale, 0.f, flags, t, coef, S, stream);
+}
+
 int fitb200_cfg_ddim_step(const float* x, const float* model_out, const float* noise, float* sample, float* pred_xstart,
-                          int rows, int64_t per_row, int cfg_pairs, float cfg_scale, float eta, const int64_t* t,
-                          const float* coef, int S, fitb200_stream_t stream) {
-  FITB200_CHECK_ARG(x && model_out && noise && sample && t && coef && rows > 0 && per_row > 0 && S > 0, "ddim_step: bad arguments");
-  FITB200_CHECK_ARG(per_row % 4 == 0, "ddim_step: per-row element count %lld must be a multiple of 4", (long long)per_row);
-  FITB200_CHECK_ARG(cfg_pairs == 0 || rows == 2 * cfg_pairs, "ddim_step: cfg_pairs must be 0 or rows/2");
-  long nvec = (long)rows * per_row / 4;
-  cfg_step_kernel<true><<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x, model_out, noise, sample, pred_xstart, rows, per_row, cfg_pairs, cfg_scale, eta, t, coef, S);
-  FITB200_CHECK_LAUNCH("ddim_step");
+                          int rows, int64_t per_row, int cfg_pairs, float cfg_scale, float eta, int flags,
+                          const int64_t* t, const float* coef, int S, fitb200_stream_t stream) {
+  return launch_step(true, x, model_out, noise, sample, pred_xstart, nullptr, rows, per_row, cfg_pairs, cfg_scale, eta, flags, t, coef, S, stream);
+}
+
+int fitb200_cfg_combine(const float* model_out, float* out, int pairs, int64_t per_row, float cfg_scale,
+                        fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(model_out && out && pairs > 0 && per_row > 0 && per_row % 4 == 0, "cfg_combine: bad arguments");
+  long nvec = (long)pairs * per_row / 4;
+  cfg_combine_kernel<<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(model_out, out, pairs, per_row, cfg_scale);
+  FITB200_CHECK_LAUNCH("cfg_combine");
   return FITB200_OK;
 }
 
@@ -481,6 +562,15 @@ int fitb200_q_sample(const float* x0, const float* noise, float* out, int rows, 
   long nvec = (long)rows * per_row / 4;
   q_sample_kernel<<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(x0, noise, out, rows, per_row, t, sqrt_ac, sqrt_1m_ac, S);
   FITB200_CHECK_LAUNCH("q_sample");
+  return FITB200_OK;
+}
+
+int fitb200_philox_normal(float* out, int rows, int64_t per_row, uint64_t seed, const int64_t* step, int64_t row_offset,
+                          fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(out && rows > 0 && per_row > 0 && per_row % 4 == 0 && row_offset >= 0, "philox_normal: bad arguments");
+  long nvec = (long)rows * per_row / 4;
+  philox_normal_kernel<<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(out, rows, per_row, seed, step, row_offset);
+  FITB200_CHECK_LAUNCH("philox_normal");
   return FITB200_OK;
 }
 

@@ -169,6 +169,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int n = n0 + c * 32;
         if (n >= p.N) break;  // warp-uniform
         float acc[32];
+        __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the row-predicated stores below
         tmem_ld32(taddr + c * 32, acc);
         if (!row_ok) continue;
         if (EPI == FITB200_EPI_SWIGLU) {

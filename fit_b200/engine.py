@@ -1,0 +1,224 @@
+"""Forward executor of the FiT network on libfit_b200.so.
+
+Sequences the C-ABI kernels for FiT.forward (reference FiT/models/fit.py:474-518): no torch
+arithmetic, no allocation after the first call for a given (rows, tokens) shape, everything on the
+current stream -- so a whole forward (and a whole sampling step) is CUDA-graph capturable.
+
+Data layout in HBM (row-major, one row per token):
+  xs   [R*T, D]   residual stream (act dtype)      h   [R*T, D]   LN+modulate output (GEMM A operand)
+  qkv  [R*T, 3D]  column = which*D + head*d + i    att [R*T, D]   attention output, heads merged
+  g    [R*T, Hp]  SwiGLU hidden                     mod [R, L*6D+2D] fp32 adaLN table of ALL blocks + final layer
+Precision modes: "bf16" (tcgen05 GEMMs, bf16 activations, fp32 accumulation / LN / softmax / modulation)
+and "fp32" (verification mode: CUDA-core fp32 GEMMs and fp32 activations).
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import ops
+from ._lib import EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_SILU, EPI_SWIGLU
+
+Tensor = torch.Tensor
+
+
+def _round_up(a: int, b: int) -> int:
+    return (a + b - 1) // b * b
+
+
+class _Weights:
+    """Device copies of the parameters in the layout the kernels want (rebuilt when parameters change)."""
+
+    def __init__(self, model, precision: str):
+        D, L = model.hidden_size, len(model.blocks)
+        H = model.blocks[0].ffn.hidden_features if L else 0
+        Hp = _round_up(H, 16)
+        self.H, self.Hp = H, Hp
+        bf16 = precision == "bf16"
+        wdt = torch.bfloat16 if bf16 else torch.float32
+
+        def f32(p):
+            return p.detach().float().contiguous()
+
+        def w(p):
+            return p.detach().to(wdt).contiguous()
+
+        self.x_w, self.x_b = f32(model.x_embedder.weight), f32(model.x_embedder.bias)
+        self.t0_w, self.t0_b = f32(model.t_embedder.mlp[0].weight), f32(model.t_embedder.mlp[0].bias)
+        self.t2_w, self.t2_b = f32(model.t_embedder.mlp[2].weight), f32(model.t_embedder.mlp[2].bias)
+        self.y_table = f32(model.y_embedder.embedding_table.weight)
+        # adaLN of every block and of the final layer as ONE [L*6D + 2D, D] weight: c is shared by all of
+        # them (fit.py:505,513; dit.py:139), so a single small-M GEMM per forward produces the whole table
+        ada_w = [b.adaLN_modulation[1].weight for b in model.blocks] + [model.final_layer.adaLN_modulation[1].weight]
+        ada_b = [b.adaLN_modulation[1].bias for b in model.blocks] + [model.final_layer.adaLN_modulation[1].bias]
+        self.ada_w = torch.cat([p.detach() for p in ada_w], 0).to(wdt).contiguous()
+        self.ada_b = torch.cat([p.detach() for p in ada_b], 0).float().contiguous()
+        self.n_mod = self.ada_w.shape[0]
+        self.blocks = []
+        for blk in model.blocks:
+            e = {}
+            e["qkv_w"], e["qkv_b"] = w(blk.attn.qkv.weight), f32(blk.attn.qkv.bias)
+            e["proj_w"], e["proj_b"] = w(blk.attn.proj.weight), f32(blk.attn.proj.bias)
+            fg, fx = blk.ffn.fc1_g, blk.ffn.fc1_x
+            if bf16:
+                # packed SwiGLU weight: 16 rows of fc1_g then the matching 16 rows of fc1_x, so one 32-column
+                # accumulator chunk of the epilogue holds gate and up of the same 16 hidden units
+                dev = fg.weight.device
+                wg = torch.zeros(Hp, D, device=dev, dtype=wdt)
+                wx = torch.zeros(Hp, D, device=dev, dtype=wdt)
+                wg[:H], wx[:H] = fg.weight.detach().to(wdt), fx.weight.detach().to(wdt)
+                bg = torch.zeros(Hp, device=dev)
+                bx = torch.zeros(Hp, device=dev)
+                bg[:H], bx[:H] = fg.bias.detach().float(), fx.bias.detach().float()
+                e["fc1_w"] = torch.stack([wg.view(Hp // 16, 16, D), wx.view(Hp // 16, 16, D)], 1).reshape(2 * Hp, D).contiguous()
+                e["fc1_b"] = torch.stack([bg.view(Hp // 16, 16), bx.view(Hp // 16, 16)], 1).reshape(2 * Hp).contiguous()
+            else:
+                e["fc1_g_w"], e["fc1_g_b"] = f32(fg.weight), f32(fg.bias)
+                e["fc1_x_w"], e["fc1_x_b"] = f32(fx.weight), f32(fx.bias)
+            w2 = blk.ffn.fc2.weight.detach()
+            if Hp != H:
+                w2p = torch.zeros(D, Hp, device=w2.device, dtype=wdt)
+                w2p[:, :H] = w2.to(wdt)
+                e["fc2_w"] = w2p
+            else:
+                e["fc2_w"] = w2.to(wdt).contiguous()
+            e["fc2_b"] = f32(blk.ffn.fc2.bias)
+            self.blocks.append(e)
+        self.fin_w, self.fin_b = f32(model.final_layer.linear.weight), f32(model.final_layer.linear.bias)
+
+
+class _Workspace:
+    def __init__(self, R: int, T: int, D: int, Hp: int, n_mod: int, act: torch.dtype, device):
+        M = R * T
+        z = dict(device=device)
+        self.R, self.T = R, T
+        self.xs = torch.empty(M, D, dtype=act, **z)
+        self.h = torch.empty(M, D, dtype=act, **z)
+        self.qkv = torch.empty(M, 3 * D, dtype=act, **z)
+        self.att = torch.empty(M, D, dtype=act, **z)
+        self.g = torch.zeros(M, Hp, dtype=act, **z)  # padded columns (FiT-L) stay zero
+        self.mod = torch.empty(R, n_mod, dtype=torch.float32, **z)
+        self.tfreq = torch.empty(R, 256, dtype=torch.float32, **z)
+        self.t1 = torch.empty(R, D, dtype=torch.float32, **z)
+        self.t2 = torch.empty(R, D, dtype=torch.float32, **z)
+        self.c = torch.empty(R, D, dtype=torch.float32, **z)
+        self.silu_c = torch.empty(R, D, dtype=act, **z)
+        self.kv_len = torch.empty(R, dtype=torch.int32, **z)
+        self.n_valid = torch.empty(R, dtype=torch.int32, **z)
+        L6 = (n_mod - 2 * D) // (6 * D)
+        # per-block views into the adaLN table: shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp
+        # (chunk order of fit.py:329-330); final layer: shift, scale (dit.py:139)
+        self.mod_views = [[self.mod[:, (6 * i + k) * D:(6 * i + k + 1) * D] for k in range(6)] for i in range(L6)]
+        self.fin_views = [self.mod[:, 6 * L6 * D + k * D: 6 * L6 * D + (k + 1) * D] for k in range(2)]
+
+
+class FiTEngine:
+    """Runs FiT.forward for one ``fit_b200.models.fit.FiT`` module."""
+
+    def __init__(self, model, precision: str = "bf16"):
+        if precision not in ("bf16", "fp32"):
+            raise ValueError("precision must be 'bf16' or 'fp32'")
+        self.model = model
+        self.precision = precision
+        self._w: Optional[_Weights] = None
+        self._w_key = None
+        self._ws: Dict[Tuple[int, int, str], _Workspace] = {}
+
+    # ------------------------------------------------------------------ caches
+    @property
+    def act_dtype(self):
+        return torch.bfloat16 if self.precision == "bf16" else torch.float32
+
+    def weights(self) -> _Weights:
+        params = list(self.model.parameters())
+        key = (self.precision,) + tuple((p.data_ptr(), p._version) for p in params)
+        if self._w is None or key != self._w_key:
+            if not params[0].is_cuda:
+                raise RuntimeError("fit_b200: the model must live on a CUDA device (no CPU fallback)")
+            self._w = _Weights(self.model, self.precision)
+            self._w_key = key
+        return self._w
+
+    def workspace(self, R: int, T: int, device) -> _Workspace:
+        key = (R, T, str(device))
+        ws = self._ws.get(key)
+        if ws is None:
+            W = self.weights()
+            if len(self._ws) >= 4:  # bounded cache: mixed-resolution callers cycle through few shapes
+                self._ws.pop(next(iter(self._ws)))
+            ws = _Workspace(R, T, self.model.hidden_size, W.Hp, W.n_mod, self.act_dtype, device)
+            self._ws[key] = ws
+        return ws
+
+    # ------------------------------------------------------------------ pieces
+    def conditioning(self, ws: _Workspace, W: _Weights, t: Tensor, y: Tensor):
+        """t_embedder + y_embedder + c = t + y (fit.py:503-505) and the adaLN table of all blocks."""
+        ops.timestep_sincos(t, ws.tfreq)
+        ops.gemm(ws.tfreq, W.t0_w, W.t0_b, ws.t1, EPI_BIAS_SILU)
+        ops.gemm(ws.t1, W.t2_w, W.t2_b, ws.t2, EPI_BIAS)
+        ops.cond_combine(ws.t2, y, W.y_table, ws.c, ws.silu_c)
+        ops.gemm(ws.silu_c, W.ada_w, W.ada_b, ws.mod, EPI_BIAS)
+
+    def block(self, i: int, ws: _Workspace, W: _Weights, pos: Tensor, mask: Optional[Tensor]):
+        """FiTBlock.forward (fit.py:326-337) in place on ws.xs."""
+        m = self.model
+        R, T, D = ws.R, ws.T, m.hidden_size
+        e = W.blocks[i]
+        sh1, sc1, g1, sh2, sc2, g2 = ws.mod_views[i]
+        nm = W.n_mod
+        ops.ln_modulate(ws.xs, sh1, sc1, nm, T, ws.h)
+        ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS)
+        ops.attention(ws.qkv, pos, ws.kv_len, mask, R, T, m.num_heads, D // m.num_heads, ws.att)
+        ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=nm, rows_per_sample=T, resid=ws.xs)
+        ops.ln_modulate(ws.xs, sh2, sc2, nm, T, ws.h)
+        if self.precision == "bf16":
+            ops.gemm(ws.h, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU)
+        else:
+            ops.gemm(ws.h, e["fc1_g_w"], e["fc1_g_b"], ws.g, EPI_SWIGLU, B2=e["fc1_x_w"], bias2=e["fc1_x_b"])
+        ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=nm, rows_per_sample=T, resid=ws.xs)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x: Tensor, t: Tensor, y: Tensor, pos: Tensor, mask: Tensor, train: bool = True,
+                rows: Optional[int] = None, out: Optional[Tensor] = None, collect: Optional[list] = None) -> Tensor:
+        """x: tokens [N,T,p*p*C] (train=True) or latents [N,C,H,W] (train=False), fp32.
+        rows: number of rows to run (>= x.shape[0], a multiple of it): row r reads x[r % x.shape[0]] --
+        forward_with_cfg's cat([half, half]) without the copy."""
+        m = self.model
+        p, C_in, D = m.patch_size, m.in_channels, m.hidden_size
+        if x.dtype != torch.float32:
+            raise TypeError("fit_b200: x must be fp32")
+        R = x.shape[0] if rows is None else rows
+        if train:
+            T = x.shape[1]
+            H = Wd = 0
+        else:
+            H, Wd = x.shape[2], x.shape[3]
+            T = (H // p) * (Wd // p)
+        if mask.shape[0] != R or mask.shape[1] != T:
+            raise ValueError(f"mask shape {tuple(mask.shape)} does not match ({R}, {T})")
+        if pos.dim() == 2:
+            pos = pos[None]
+        if pos.shape[0] not in (1, R) or pos.shape[1] != T or pos.shape[2] != D // m.num_heads:
+            raise ValueError(f"pos shape {tuple(pos.shape)} does not match (1|{R}, {T}, {D // m.num_heads})")
+        if pos.dtype != torch.float32:
+            raise TypeError("fit_b200: pos must be fp32 (cos, sin) pairs")
+        W = self.weights()
+        ws = self.workspace(R, T, x.device)
+        t = t.to(torch.int64) if t.dtype != torch.int64 else t
+        y = y.to(torch.int64) if y.dtype != torch.int64 else y
+        ops.mask_to_kvlen(mask, ws.kv_len, ws.n_valid)
+        ops.embed_tokens(x, W.x_w, W.x_b, ws.xs, R, T, p, C_in)
+        self.conditioning(ws, W, t, y)
+        if collect is not None:
+            collect.append(ws.xs.float().view(R, T, D).clone())
+        for i in range(len(m.blocks)):
+            self.block(i, ws, W, pos, mask)
+            if collect is not None:
+                collect.append(ws.xs.float().view(R, T, D).clone())
+        P = p * p * m.out_channels
+        if out is None:
+            out = torch.empty((R, T, P) if train else (R, m.out_channels, H, Wd), dtype=torch.float32, device=x.device)
+        sh, sc = ws.fin_views
+        ops.final_layer(ws.xs, sh, sc, W.n_mod, W.fin_w, W.fin_b, out, R, T, p, m.out_channels)
+        return out

@@ -1,0 +1,203 @@
+"""Tensor-level wrappers over the C ABI: argument checking, pointers, the current CUDA stream.
+
+Each function enqueues one kernel of libfit_b200.so on ``torch.cuda.current_stream()``; the caller
+allocates outputs (these helpers allocate only when ``out`` is None).  No torch arithmetic here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+from ._lib import BF16, EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_SILU, EPI_SWIGLU, F32  # noqa: F401
+
+Tensor = torch.Tensor
+
+
+def _c(t: Tensor) -> Tensor:
+    if not t.is_contiguous():
+        raise ValueError("fit_b200: tensor must be contiguous")
+    return t
+
+
+def mask_to_kvlen(mask: Tensor, kv_len: Optional[Tensor] = None, n_valid: Optional[Tensor] = None):
+    L.require_cuda(mask)
+    R, T = mask.shape
+    m8 = _c(mask.view(torch.uint8) if mask.dtype == torch.bool else mask)
+    if kv_len is None:
+        kv_len = torch.empty(R, dtype=torch.int32, device=mask.device)
+    if n_valid is None:
+        n_valid = torch.empty(R, dtype=torch.int32, device=mask.device)
+    L.check(L.lib().fitb200_mask_to_kvlen(L.ptr(m8), R, T, L.ptr(kv_len), L.ptr(n_valid), L.stream_ptr()), "mask_to_kvlen")
+    return kv_len, n_valid
+
+
+def embed_tokens(x: Tensor, w: Tensor, b: Tensor, out: Tensor, R: int, T: int, p: int, C_in: int):
+    """x: tokens [R_src,T,p*p*C] or latents [R_src,C,H,W] (fp32) -> out [R,T,D] (row r reads r % R_src)."""
+    L.require_cuda(x, w, b, out)
+    nchw = x.dim() == 4
+    R_src = x.shape[0]
+    H, W = (x.shape[2], x.shape[3]) if nchw else (0, 0)
+    D = w.shape[0]
+    L.check(L.lib().fitb200_embed_tokens_fwd(L.ptr(_c(x)), int(nchw), R, R_src, C_in, H, W, p, T, L.ptr(_c(w)), L.ptr(_c(b)),
+                                             D, L.ptr(out), L.dtype_code(out), L.stream_ptr()), "embed_tokens")
+    return out
+
+
+def timestep_sincos(t: Tensor, out: Tensor, freqs: Optional[Tensor] = None):
+    L.require_cuda(t, out)
+    assert t.dtype == torch.int64 and out.dtype == torch.float32
+    L.check(L.lib().fitb200_timestep_sincos(L.ptr(_c(t)), t.shape[0], L.ptr(freqs), L.ptr(out), L.stream_ptr()), "timestep_sincos")
+    return out
+
+
+def cond_combine(t_emb: Tensor, y: Tensor, table: Tensor, c: Optional[Tensor], silu_c: Tensor):
+    L.require_cuda(t_emb, y, table, silu_c)
+    R, D = silu_c.shape
+    assert y.dtype == torch.int64 and t_emb.dtype == torch.float32 and table.dtype == torch.float32
+    L.check(L.lib().fitb200_cond_combine_fwd(L.ptr(_c(t_emb)), t_emb.shape[0], L.ptr(_c(y)), L.ptr(_c(table)), table.shape[0],
+                                             R, D, L.ptr(c), L.ptr(silu_c), L.dtype_code(silu_c), L.stream_ptr()), "cond_combine")
+    return silu_c
+
+
+def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: int = EPI_BIAS, *, M: Optional[int] = None,
+         B2: Optional[Tensor] = None, bias2: Optional[Tensor] = None, gate: Optional[Tensor] = None, ld_gate: int = 0,
+         rows_per_sample: int = 1, resid: Optional[Tensor] = None, N: Optional[int] = None):
+    """out = epilogue(A @ B^T).  A [M,K] and B [N,K] both fp32 (CUDA-core path) or both bf16 (tcgen05 path).
+    ``gate`` may be a strided view: pass the storage-offset view and its row stride ``ld_gate``."""
+    L.require_cuda(A, B, out)
+    a = L.GemmArgs()
+    a.M = A.shape[0] if M is None else M
+    a.K = A.shape[1]
+    a.N = B.shape[0] if N is None else N
+    a.A, a.lda = A.data_ptr(), A.stride(0)
+    a.B, a.ldb = B.data_ptr(), B.stride(0)
+    a.B2 = 0 if B2 is None else B2.data_ptr()
+    a.bias = 0 if bias is None else bias.data_ptr()
+    a.bias2 = 0 if bias2 is None else bias2.data_ptr()
+    a.out, a.ldo, a.out_dtype = out.data_ptr(), out.stride(0), L.dtype_code(out)
+    a.epilogue = epilogue
+    a.gate = 0 if gate is None else gate.data_ptr()
+    a.ld_gate, a.rows_per_sample = ld_gate, rows_per_sample
+    a.resid = 0 if resid is None else resid.data_ptr()
+    a.ld_resid = 0 if resid is None else resid.stride(0)
+    a.resid_dtype = F32 if resid is None else L.dtype_code(resid)
+    if A.dtype == torch.float32 and B.dtype == torch.float32:
+        fn, what = L.lib().fitb200_gemm_f32, "gemm_f32"
+    elif A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16:
+        fn, what = L.lib().fitb200_gemm_bf16_tc, "gemm_bf16_tc"
+    else:
+        raise TypeError(f"fit_b200.gemm: A {A.dtype} / B {B.dtype} must both be fp32 or both bf16")
+    L.check(fn(C.byref(a), L.stream_ptr()), what)
+    return out
+
+
+def ln_modulate(x: Tensor, shift: Tensor, scale: Tensor, ld_mod: int, rows_per_sample: int, out: Tensor,
+                mean: Optional[Tensor] = None, rstd: Optional[Tensor] = None):
+    """out = LN(x) * (1 + scale[s]) + shift[s]; x, out: [M, D]; shift/scale: fp32 views with row stride ld_mod."""
+    L.require_cuda(x, shift, scale, out)
+    M, D = x.shape
+    L.check(L.lib().fitb200_ln_modulate_fwd(L.ptr(_c(x)), L.dtype_code(x), M, D, rows_per_sample, L.ptr(shift), L.ptr(scale),
+                                            ld_mod, L.ptr(out), L.dtype_code(out), L.ptr(mean), L.ptr(rstd), L.stream_ptr()),
+            "ln_modulate")
+    return out
+
+
+def attention(qkv: Tensor, freqs: Tensor, kv_len: Tensor, mask: Optional[Tensor], R: int, T: int, h: int, d: int,
+              out: Tensor, lse: Optional[Tensor] = None):
+    """qkv [R*T, 3*h*d] -> out [R*T, h*d]; RoPE + key-masked softmax attention."""
+    L.require_cuda(qkv, freqs, kv_len, out)
+    assert freqs.dtype == torch.float32 and kv_len.dtype == torch.int32
+    m8 = None
+    if mask is not None:
+        m8 = _c(mask.view(torch.uint8) if mask.dtype == torch.bool else mask)
+    fr = 1 if freqs.dim() == 2 else freqs.shape[0]
+    L.check(L.lib().fitb200_attn_fwd(L.ptr(_c(qkv)), L.dtype_code(qkv), L.ptr(_c(freqs)), fr, L.ptr(kv_len), L.ptr(m8), R, T, h, d,
+                                     L.ptr(out), L.ptr(lse), L.stream_ptr()), "attn_fwd")
+    return out
+
+
+def final_layer(x: Tensor, shift: Tensor, scale: Tensor, ld_mod: int, w: Tensor, b: Tensor, out: Tensor, R: int, T: int,
+                p: int, C_out: int):
+    """x [R*T, D] -> out tokens [R,T,P] or latents [R,C,H,W] (decided by out.dim())."""
+    L.require_cuda(x, shift, scale, w, b, out)
+    D = x.shape[-1]
+    P = w.shape[0]
+    nchw = out.dim() == 4
+    H, W = (out.shape[2], out.shape[3]) if nchw else (0, 0)
+    assert out.dtype == torch.float32 and w.dtype == torch.float32
+    L.check(L.lib().fitb200_final_layer_fwd(L.ptr(_c(x)), L.dtype_code(x), R, T, D, L.ptr(shift), L.ptr(scale), ld_mod, L.ptr(_c(w)),
+                                            L.ptr(_c(b)), P, L.ptr(out), int(nchw), C_out, H, W, p, L.stream_ptr()), "final_layer")
+    return out
+
+
+STEP_CLIP_DENOISED, STEP_PREDICT_XSTART = 1, 2
+
+
+def cfg_step(x: Tensor, model_out: Tensor, noise: Optional[Tensor], t: Tensor, coef: Tensor, *, cfg_pairs: int = 0,
+             cfg_scale: float = 1.0, ddim: bool = False, eta: float = 0.0, flags: int = 0, sample: Optional[Tensor] = None,
+             pred_xstart: Optional[Tensor] = None, mean: Optional[Tensor] = None, want_sample: bool = True):
+    """Fused (CFG combine +) DDPM / DDIM update.  Returns (sample, pred_xstart, mean)."""
+    L.require_cuda(x, model_out, t, coef)
+    assert x.dtype == torch.float32 and model_out.dtype == torch.float32
+    assert noise is None or noise.dtype == torch.float32
+    assert t.dtype == torch.int64 and coef.dtype == torch.float32 and coef.shape[1] == 8
+    rows = x.shape[0]
+    per_row = x.numel() // rows
+    if sample is None and want_sample:
+        sample = torch.empty_like(x)
+    S = coef.shape[0]
+    noise = None if noise is None else _c(noise)
+    if ddim:
+        rc = L.lib().fitb200_cfg_ddim_step(L.ptr(_c(x)), L.ptr(_c(model_out)), L.ptr(noise), L.ptr(sample), L.ptr(pred_xstart),
+                                           rows, per_row, cfg_pairs, cfg_scale, eta, flags, L.ptr(_c(t)), L.ptr(_c(coef)), S,
+                                           L.stream_ptr())
+    else:
+        rc = L.lib().fitb200_cfg_ddpm_step(L.ptr(_c(x)), L.ptr(_c(model_out)), L.ptr(noise), L.ptr(sample), L.ptr(pred_xstart),
+                                           L.ptr(mean), rows, per_row, cfg_pairs, cfg_scale, flags, L.ptr(_c(t)),
+                                           L.ptr(_c(coef)), S, L.stream_ptr())
+    L.check(rc, "cfg_step")
+    return sample, pred_xstart, mean
+
+
+def cfg_combine(model_out: Tensor, cfg_scale: float, out: Optional[Tensor] = None):
+    """forward_with_cfg's eps combine: rows [0,B) cond, [B,2B) uncond -> both halves = u + s (c - u)."""
+    L.require_cuda(model_out)
+    pairs = model_out.shape[0] // 2
+    if out is None:
+        out = torch.empty_like(model_out)
+    L.check(L.lib().fitb200_cfg_combine(L.ptr(_c(model_out)), L.ptr(out), pairs, model_out.numel() // model_out.shape[0],
+                                        float(cfg_scale), L.stream_ptr()), "cfg_combine")
+    return out
+
+
+def q_sample(x0: Tensor, noise: Tensor, t: Tensor, sqrt_ac: Tensor, sqrt_1m_ac: Tensor, out: Optional[Tensor] = None):
+    L.require_cuda(x0, noise, t, sqrt_ac, sqrt_1m_ac)
+    rows = x0.shape[0]
+    if out is None:
+        out = torch.empty_like(x0)
+    L.check(L.lib().fitb200_q_sample(L.ptr(_c(x0)), L.ptr(_c(noise)), L.ptr(out), rows, x0.numel() // rows, L.ptr(_c(t)),
+                                     L.ptr(sqrt_ac), L.ptr(sqrt_1m_ac), sqrt_ac.shape[0], L.stream_ptr()), "q_sample")
+    return out
+
+
+def philox_normal(out: Tensor, seed: int, step: Optional[Tensor], row_offset: int = 0):
+    """out[rows, ...] <- N(0,1) keyed by (seed, step[0], global row index)."""
+    L.require_cuda(out)
+    assert out.dtype == torch.float32 and out.is_contiguous()
+    rows = out.shape[0]
+    L.check(L.lib().fitb200_philox_normal(L.ptr(out), rows, out.numel() // rows, seed & (2 ** 64 - 1), L.ptr(step), row_offset,
+                                          L.stream_ptr()), "philox_normal")
+    return out
+
+
+def gather_i64(table: Tensor, idx: Tensor, out: Tensor):
+    L.check(L.lib().fitb200_gather_i64(L.ptr(table), table.shape[0], L.ptr(idx), L.ptr(out), idx.shape[0], L.stream_ptr()), "gather_i64")
+    return out
+
+
+def add_i64(idx: Tensor, delta: int):
+    L.check(L.lib().fitb200_add_i64(L.ptr(idx), idx.shape[0], int(delta), L.stream_ptr()), "add_i64")
+    return idx

@@ -1,0 +1,126 @@
+"""CUDA-graph sampling loop: the caller side of the hot path (sample_lightning.py:36-70 of the reference).
+
+One denoising step = [loop index -> model timestep gather] + [FiT forward on 2B rows: B conditional | B null-class]
++ [Philox noise] + [fused CFG + DDPM/DDIM update of the B latents] + [index decrement], captured ONCE as a CUDA
+graph and replayed ``num_timesteps`` times: no per-step host-to-device copy (the reference does ~8 per step:
+gaussian_diffusion.py:679,882-894; respace.py:125), no per-step allocation, no Python between kernels.
+
+Only the B latents the reference keeps (``samples, _ = samples.chunk(2)``, sample_lightning.py:69) are carried;
+the duplicated half of forward_with_cfg's input (fit.py:545-546) is produced by the embed kernel's row
+replication, not by a copy.  Noise is keyed by (seed, step, global image index): a batch sharded over N GPUs
+(``row_offset``) reproduces the single-GPU images bit for bit, with no collective.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import ops
+
+Tensor = torch.Tensor
+
+
+class CFGSampler:
+    def __init__(self, model, diffusion, batch: int, latent_hw: Tuple[int, int], cfg_scale: float = 1.5, seed: int = 0,
+                 row_offset: int = 0, mode: str = "ddpm", eta: float = 0.0, clip_denoised: bool = False,
+                 use_graph: bool = True, device=None):
+        if mode not in ("ddpm", "ddim"):
+            raise ValueError("mode must be 'ddpm' or 'ddim'")
+        self.model, self.diffusion = model, diffusion
+        self.B = batch
+        self.cfg_scale, self.seed, self.row_offset = float(cfg_scale), int(seed), int(row_offset)
+        self.mode, self.eta, self.clip = mode, float(eta), bool(clip_denoised)
+        dev = device or next(model.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("fit_b200: the sampler needs a CUDA device (no CPU fallback)")
+        self.device = dev
+        H, W = latent_hw
+        p, C = model.patch_size, model.in_channels
+        self.T = (H // p) * (W // p)
+        self.d = model.hidden_size // model.num_heads
+        B = batch
+        self.x = torch.empty(B, C, H, W, dtype=torch.float32, device=dev)           # the B latents, updated in place
+        self.raw = torch.empty(2 * B, model.out_channels, H, W, dtype=torch.float32, device=dev)
+        self.noise = torch.empty(B, C, H, W, dtype=torch.float32, device=dev)
+        self.y = torch.empty(2 * B, dtype=torch.int64, device=dev)                   # labels | null class
+        self.pos = torch.empty(1, self.T, self.d, dtype=torch.float32, device=dev)
+        self.pos_rows = 1
+        self.mask = torch.ones(2 * B, self.T, dtype=torch.bool, device=dev)
+        self.t_idx = torch.empty(2 * B, dtype=torch.int64, device=dev)               # loop index i (respaced)
+        self.t_model = torch.empty(2 * B, dtype=torch.int64, device=dev)             # original timestep fed to the model
+        self.step_scalar = torch.empty(1, dtype=torch.int64, device=dev)
+        self.use_graph = use_graph
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self.launches_per_step = 0
+
+    # ------------------------------------------------------------------ one step (all C-ABI launches)
+    def _step(self):
+        d, m = self.diffusion, self.model
+        tb = d._tables(self.device)
+        ops.gather_i64(d._map_tensor(self.device), self.t_idx, self.t_model)
+        m.engine.forward(self.x, self.t_model, self.y, self.pos, self.mask, train=False, rows=2 * self.B, out=self.raw)
+        ops.philox_normal(self.noise, self.seed, self.t_idx, self.row_offset)
+        ops.cfg_step(self.x, self.raw, self.noise, self.t_idx[: self.B], tb["coef"], cfg_pairs=self.B, cfg_scale=self.cfg_scale,
+                     ddim=(self.mode == "ddim"), eta=self.eta, flags=d._flags(self.clip), sample=self.x)
+        ops.add_i64(self.t_idx, -1)
+
+    def kernels_per_step(self) -> int:
+        """Number of libfit_b200 kernel launches in one step (7 per block + embed/conditioning/final + 5 loop kernels)."""
+        L = len(self.model.blocks)
+        return 7 * L + 8 + 4
+
+    def noise_for_step(self, i: int, row_offset: int = 0, rows: Optional[int] = None) -> Tensor:
+        rows = self.B if rows is None else rows
+        out = torch.empty(rows, *self.x.shape[1:], dtype=torch.float32, device=self.device)
+        self.step_scalar.fill_(i)
+        return ops.philox_normal(out, self.seed, self.step_scalar, self.row_offset + row_offset)
+
+    # ------------------------------------------------------------------ driver
+    def load(self, z: Tensor, y: Tensor, pos: Tensor, mask: Optional[Tensor] = None):
+        """Stage one batch: z [B,C,H,W] (host or device), labels [B], RoPE table [1|2B, T, d], optional mask [2B, T]."""
+        B = self.B
+        self.x.copy_(z, non_blocking=True)
+        self.y[:B].copy_(y, non_blocking=True)
+        self.y[B:].fill_(self.model.y_embedder.num_classes)   # null class id (sample_lightning.py:40)
+        pos = pos if pos.dim() == 3 else pos[None]
+        if pos.shape[0] != self.pos.shape[0]:
+            self.pos = torch.empty(pos.shape, dtype=torch.float32, device=self.device)
+            self._graph = None
+        self.pos.copy_(pos, non_blocking=True)
+        if mask is not None:
+            self.mask.copy_(mask, non_blocking=True)
+        else:
+            self.mask.fill_(True)
+        self.t_idx.fill_(self.diffusion.num_timesteps - 1)
+
+    def run(self, steps: Optional[int] = None):
+        """Enqueue `steps` denoising steps (default: all remaining) on the current stream."""
+        n = self.diffusion.num_timesteps if steps is None else steps
+        with torch.no_grad():
+            if not self.use_graph:
+                for _ in range(n):
+                    self._step()
+                return
+            if self._graph is None:
+                # warm-up outside capture: workspace allocation, weight packing, cudaFuncSetAttribute
+                saved = (self.x.clone(), self.t_idx.clone())
+                self._step()
+                torch.cuda.synchronize(self.device)
+                self.x.copy_(saved[0]); self.t_idx.copy_(saved[1])
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._step()
+                self._graph = g
+                self.x.copy_(saved[0]); self.t_idx.copy_(saved[1])
+            for _ in range(n):
+                self._graph.replay()
+
+    def sample(self, z: Tensor, y: Tensor, pos: Tensor, mask: Optional[Tensor] = None, out: Optional[Tensor] = None) -> Tensor:
+        """Full loop: returns the B final latents (a fresh device tensor, or copied into `out`, e.g. pinned host memory)."""
+        self.load(z, y, pos, mask)
+        self.run()
+        if out is None:
+            return self.x.clone()
+        out.copy_(self.x, non_blocking=True)
+        return out

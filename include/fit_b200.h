@@ -133,23 +133,42 @@ int fitb200_final_layer_fwd(const void* x, int x_dtype, int R, int T, int D, con
  * _extract_into_tensor does (:891).
  * cfg_pairs = B > 0: model_out holds the raw network output for rows [0,B) conditional and [B,2B)
  * unconditional and the classifier-free-guidance combine of forward_with_cfg (fit.py:549-552) is
- * applied on the fly: eps[r] = u + s (c - u) with pair index r % B.  cfg_pairs = 0: model_out is eps.
+ * applied on the fly: eps[r] = u + s (c - u) with pair index r % B; x / noise / sample then have
+ * rows = 2B (the reference's duplicated batch) or rows = B (only the half the reference keeps,
+ * sample_lightning.py:69).  cfg_pairs = 0: model_out is eps.
  * ddpm: p_mean_variance EPSILON branch, clip_denoised=False (:332-335,346-351,244-264) + p_sample (:422-428):
  *   x0 = c0 x - c1 eps;  mean = c2 x0 + c3 x;  sample = mean + (t != 0) exp(0.5 logvar) noise.
  * ddim (:553-572): eps' re-derived from x0, sigma = eta sqrt((1-ab_prev)/(1-ab)) sqrt(1-ab/ab_prev),
  *   sample = sqrt(ab_prev) x0 + sqrt(1-ab_prev-sigma^2) eps' + (t != 0) sigma noise.
- * t: device int64 [rows] indices into coef.  pred_xstart nullable.  sample may alias x. */
+ * flags: FITB200_STEP_CLIP_DENOISED clamps x0 to [-1,1] (process_xstart, :322-326);
+ *        FITB200_STEP_PREDICT_XSTART: the model output is x0 itself (START_X, :328-331).
+ * t: device int64 [rows] indices into coef.  noise may be NULL (= 0).  sample / pred_xstart / mean
+ * (the posterior mean p_mean_variance returns, :335) are each nullable; sample may alias x. */
+enum { FITB200_STEP_CLIP_DENOISED = 1, FITB200_STEP_PREDICT_XSTART = 2 };
 int fitb200_cfg_ddpm_step(const float* x, const float* model_out, const float* noise, float* sample,
-                          float* pred_xstart, int rows, int64_t per_row, int cfg_pairs, float cfg_scale,
-                          const int64_t* t, const float* coef, int S, fitb200_stream_t stream);
+                          float* pred_xstart, float* mean, int rows, int64_t per_row, int cfg_pairs, float cfg_scale,
+                          int flags, const int64_t* t, const float* coef, int S, fitb200_stream_t stream);
 int fitb200_cfg_ddim_step(const float* x, const float* model_out, const float* noise, float* sample,
                           float* pred_xstart, int rows, int64_t per_row, int cfg_pairs, float cfg_scale, float eta,
-                          const int64_t* t, const float* coef, int S, fitb200_stream_t stream);
+                          int flags, const int64_t* t, const float* coef, int S, fitb200_stream_t stream);
+
+/* forward_with_cfg's combine alone (fit.py:549-553): model_out rows [0,pairs) conditional, [pairs,2 pairs)
+ * unconditional; out[r] = out[r + pairs] = u + s (c - u).  out must not alias model_out. */
+int fitb200_cfg_combine(const float* model_out, float* out, int pairs, int64_t per_row, float cfg_scale,
+                        fitb200_stream_t stream);
 
 /* q_sample (gaussian_diffusion.py:227-242) = DDIMScheduler.add_noise call site (FiT/train.py:53):
  * out = a[t] x0 + b[t] noise with a = sqrt_alphas_cumprod, b = sqrt_one_minus_alphas_cumprod (fp32 [S]). */
 int fitb200_q_sample(const float* x0, const float* noise, float* out, int rows, int64_t per_row, const int64_t* t,
                      const float* sqrt_ac, const float* sqrt_1m_ac, int S, fitb200_stream_t stream);
+
+/* Per-step Gaussian noise of p_sample (th.randn_like, gaussian_diffusion.py:422) as a counter-based generator:
+ * Philox4x32-10 keyed by (seed, *step), counter = (row_offset + row) * per_row/4 + i, Box-Muller -> N(0,1).
+ * Keyed by the GLOBAL image index so that a batch sharded over several GPUs draws, per image, exactly the
+ * noise of the unsharded run; `step` is read from device memory (CUDA-graph replay).  Not the torch
+ * generator's stream: parity tests pass the reference's noise explicitly instead. */
+int fitb200_philox_normal(float* out, int rows, int64_t per_row, uint64_t seed, const int64_t* step, int64_t row_offset,
+                          fitb200_stream_t stream);
 
 /* loop plumbing for CUDA-graph replay of the sampling loop (gaussian_diffusion.py:679, respace.py:125-126):
  * out[i] = map[clamp(idx[i])]; and idx[i] += delta. */

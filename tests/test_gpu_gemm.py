@@ -1,0 +1,126 @@
+"""GPU parity of the GEMM kernels (family 1): fp32 CUDA-core verification GEMM and the bf16 tcgen05 GEMM,
+every fused epilogue, tile tails in M / N / K.  Floating point: the checker is fp64 math on the same
+(bf16-rounded) inputs; tolerance = output rounding (fp32 1e-5, bf16 4e-3 relative L2)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+EPI_BIAS, EPI_BIAS_SILU, EPI_BIAS_GATE_RESID, EPI_SWIGLU = 0, 1, 2, 3
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from fit_b200 import ops as _ops
+    return _ops
+
+
+def _inputs(M, N, K, seed, wdt):
+    g = torch.Generator().manual_seed(seed)
+    A = torch.randn(M, K, generator=g).to(wdt)
+    B = (torch.randn(N, K, generator=g) / K ** 0.5).to(wdt)
+    bias = torch.randn(N, generator=g) * 0.1
+    return A, B, bias
+
+
+SHAPES = [(128, 128, 64), (256, 384, 1152), (200, 3456, 1152), (1000, 1152, 3072), (77, 776, 72), (8, 2304, 768),
+          (512, 256, 2736)]
+
+
+@pytest.mark.parametrize("wdt,odt", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16), (torch.bfloat16, torch.float32)])
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_bias_and_silu(ops, wdt, odt, M, N, K):
+    A, B, bias = _inputs(M, N, K, M + N + K, wdt)
+    want = A.double() @ B.double().t() + bias.double()
+    tol = 1e-5 if odt == torch.float32 else 4e-3
+    out = torch.empty(M, N, dtype=odt, device="cuda")
+    ops.gemm(A.cuda(), B.cuda(), bias.cuda(), out, EPI_BIAS)
+    assert rel_l2(out.float(), want) < tol
+    ops.gemm(A.cuda(), B.cuda(), bias.cuda(), out, EPI_BIAS_SILU)
+    assert rel_l2(out.float(), F.silu(want)) < tol
+
+
+@pytest.mark.parametrize("wdt,adt", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16), (torch.bfloat16, torch.float32)])
+@pytest.mark.parametrize("M,N,K,rps", [(512, 1152, 1152, 256), (400, 768, 2048, 200), (128, 128, 64, 64), (96, 144, 384, 32),
+                                       (1024, 1152, 3072, 256)])
+def test_gemm_gate_residual(ops, wdt, adt, M, N, K, rps):
+    A, B, bias = _inputs(M, N, K, M + N, wdt)
+    g = torch.Generator().manual_seed(1)
+    R = M // rps
+    mod = torch.randn(R, 3 * N, generator=g)
+    resid = torch.randn(M, N, generator=g).to(adt)
+    gate = mod[:, N:2 * N]
+    want = resid.double() + gate.double().repeat_interleave(rps, 0) * (A.double() @ B.double().t() + bias.double())
+    modc = mod.cuda()
+    xs = resid.cuda().clone()
+    # in place on the residual stream, gate is a strided view into the adaLN table
+    ops.gemm(A.cuda(), B.cuda(), bias.cuda(), xs, EPI_BIAS_GATE_RESID, gate=modc[:, N:2 * N], ld_gate=3 * N,
+             rows_per_sample=rps, resid=xs)
+    assert rel_l2(xs.float(), want) < (1e-5 if adt == torch.float32 else 4e-3)
+
+
+@pytest.mark.parametrize("M,K,H", [(256, 1152, 3072), (200, 768, 2048), (130, 128, 341), (64, 1024, 2730)])
+def test_gemm_swiglu_fp32(ops, M, K, H):
+    g = torch.Generator().manual_seed(H)
+    A = torch.randn(M, K, generator=g)
+    Wg, Wx = torch.randn(H, K, generator=g) / K ** 0.5, torch.randn(H, K, generator=g) / K ** 0.5
+    bg, bx = torch.randn(H, generator=g) * 0.1, torch.randn(H, generator=g) * 0.1
+    want = F.silu(A.double() @ Wg.double().t() + bg.double()) * (A.double() @ Wx.double().t() + bx.double())
+    Hp = (H + 15) // 16 * 16
+    out = torch.zeros(M, Hp, device="cuda")
+    ops.gemm(A.cuda(), Wg.cuda(), bg.cuda(), out, EPI_SWIGLU, B2=Wx.cuda(), bias2=bx.cuda())
+    assert rel_l2(out[:, :H], want) < 1e-5
+    assert float(out[:, H:].abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("M,K,H", [(256, 1152, 3072), (200, 768, 2048), (130, 128, 341), (64, 1024, 2730)])
+def test_gemm_swiglu_bf16_packed(ops, M, K, H):
+    """Packed [2*Hp, K] weight: 16 rows of fc1_g then the matching 16 rows of fc1_x (the engine's layout)."""
+    g = torch.Generator().manual_seed(H + 1)
+    A = torch.randn(M, K, generator=g).bfloat16()
+    Wg = (torch.randn(H, K, generator=g) / K ** 0.5).bfloat16()
+    Wx = (torch.randn(H, K, generator=g) / K ** 0.5).bfloat16()
+    bg, bx = torch.randn(H, generator=g) * 0.1, torch.randn(H, generator=g) * 0.1
+    want = F.silu(A.double() @ Wg.double().t() + bg.double()) * (A.double() @ Wx.double().t() + bx.double())
+    Hp = (H + 15) // 16 * 16
+    wg, wx = torch.zeros(Hp, K, dtype=torch.bfloat16), torch.zeros(Hp, K, dtype=torch.bfloat16)
+    wg[:H], wx[:H] = Wg, Wx
+    b1, b2 = torch.zeros(Hp), torch.zeros(Hp)
+    b1[:H], b2[:H] = bg, bx
+    Wp = torch.stack([wg.view(Hp // 16, 16, K), wx.view(Hp // 16, 16, K)], 1).reshape(2 * Hp, K).contiguous()
+    bp = torch.stack([b1.view(Hp // 16, 16), b2.view(Hp // 16, 16)], 1).reshape(2 * Hp).contiguous()
+    out = torch.empty(M, Hp, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(A.cuda(), Wp.cuda(), bp.cuda(), out, EPI_SWIGLU)
+    assert rel_l2(out[:, :H].float(), want) < 4e-3
+    assert float(out[:, H:].float().abs().sum()) == 0.0
+
+
+def test_gemm_tc_large_persistent(ops):
+    """More tiles than SMs (persistent loop, both TMEM accumulator stages, smem ring wrap-around)."""
+    M, N, K = 4096, 3456, 1152
+    A, B, bias = _inputs(M, N, K, 5, torch.bfloat16)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(A.cuda(), B.cuda(), bias.cuda(), out, EPI_BIAS)
+    want = (A.cuda().float() @ B.cuda().float().t() + bias.cuda())   # checker at size: fp32 matmul on the same inputs
+    assert rel_l2(out.float(), want) < 4e-3
+    # linearity (size-independent property): gemm(2A) - bias == 2 (gemm(A) - bias) up to bf16 rounding
+    out2 = torch.empty(M, N, dtype=torch.float32, device="cuda")
+    out1 = torch.empty(M, N, dtype=torch.float32, device="cuda")
+    ops.gemm((A * 2).cuda(), B.cuda(), None, out2, EPI_BIAS)
+    ops.gemm(A.cuda(), B.cuda(), None, out1, EPI_BIAS)
+    assert torch.equal(out2, out1 * 2)
+
+
+def test_gemm_argument_errors(ops):
+    A = torch.zeros(8, 12, dtype=torch.bfloat16, device="cuda")
+    B = torch.zeros(16, 12, dtype=torch.bfloat16, device="cuda")
+    out = torch.zeros(8, 16, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError, match="multiples of 8"):
+        ops.gemm(A, B, None, out, EPI_BIAS)
+    with pytest.raises(TypeError):
+        ops.gemm(A.float(), B, None, out, EPI_BIAS)
+    with pytest.raises(RuntimeError, match="CUDA tensors"):
+        ops.gemm(A.cpu(), B.cpu(), None, out.cpu(), EPI_BIAS)

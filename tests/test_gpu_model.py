@@ -1,0 +1,169 @@
+"""GPU parity of the whole FiT forward and of the sampling loops against fixtures generated from the
+unmodified reference (tests/golden, oracle/make_goldens.py) and against the CPU oracle.
+
+Tolerances (north_star): fp32 verification mode <= 1e-4 relative L2; bf16 mode <= 1e-2 per block
+(teacher-forced) -- valid tokens only (padded-token outputs of the reference are unspecified)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import TINY64, TINY72, TINY_SHAPES, build_model, golden, rel_l2
+from oracle import diffusion_oracle as do
+from oracle import fit_oracle as fo
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _valid_rel(out, want, mask):
+    return rel_l2(torch.as_tensor(out).cpu()[mask], torch.as_tensor(want)[mask])
+
+
+@pytest.mark.parametrize("name,cfg", [("fit_tiny_d64", TINY64), ("fit_tiny_d72", TINY72)])
+@pytest.mark.parametrize("precision,tol_out,tol_block", [("fp32", 1e-4, 1e-4), ("bf16", 2e-2, 1e-2)])
+def test_tiny_forward_matches_reference(name, cfg, precision, tol_out, tol_block):
+    z = golden(name)
+    sd = fo.random_state_dict(cfg, seed=7)
+    d = cfg["hidden_size"] // cfg["num_heads"]
+    x, t, y, pos, mask, target = synth.mixed_batch(cfg, TINY_SHAPES, 64, seed=11, rope_dim=d)
+    model = build_model(cfg, sd, precision)
+    with torch.no_grad():
+        streams = []
+        out = model.engine.forward(x.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda(), train=True, collect=streams)
+    assert _valid_rel(out, z["out_train"], mask) < tol_out
+    # per-block streams, free-running
+    ref_streams = z["streams"]
+    assert len(streams) == ref_streams.shape[0]
+    for i, s in enumerate(streams):
+        assert _valid_rel(s, ref_streams[i], mask) < tol_out, f"stream {i}"
+    # teacher-forced per-block check: block i fed with the reference's own block input
+    eng = model.engine
+    W = eng.weights()
+    ws = eng.workspace(x.shape[0], 64, torch.device("cuda", torch.cuda.current_device()))
+    for i in range(cfg["depth"]):
+        ws.xs.copy_(torch.tensor(ref_streams[i]).reshape(-1, cfg["hidden_size"]).to(ws.xs.dtype))
+        eng.block(i, ws, W, pos.cuda(), mask.cuda())
+        got = ws.xs.float().view(x.shape[0], 64, -1)
+        assert _valid_rel(got, ref_streams[i + 1], mask) < tol_block, f"block {i}"
+    # eval path (NCHW in/out) and forward_with_cfg
+    h, w = TINY_SHAPES[0]
+    zz, tt, yy, pos_e, mask_e = synth.eval_batch(cfg, h, w, 64)
+    with torch.no_grad():
+        oe = model(zz.cuda(), tt.cuda(), yy.cuda(), pos_e.cuda(), mask_e.cuda(), train=False)
+        oc = model.forward_with_cfg(zz.cuda(), tt.cuda(), yy.cuda(), pos_e.cuda(), mask_e.cuda(), 1.5)
+    assert rel_l2(oe, z["out_eval"]) < tol_out
+    assert rel_l2(oc, z["out_cfg"]) < tol_out
+    assert torch.equal(oc[:2], oc[2:])
+
+
+@pytest.mark.parametrize("name,model_name,shapes", [("fit_b2_mixed", "FiT-B/2", [(32, 32), (20, 40), (16, 64)]),
+                                                    ("fit_xl2_small", "FiT-XL/2", [(32, 32), (20, 40)])])
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16", 2e-2)])
+def test_real_width_forward_matches_reference(name, model_name, shapes, precision, tol):
+    """BASELINE config 2 (FiT-B/2 mixed resolution 256^2 / 160x320 / 128x512 padded to 256 tokens) and FiT-XL/2."""
+    z = golden(name)
+    cfg = fo.model_config(model_name)
+    sd = fo.random_state_dict(cfg, seed=7)
+    d = cfg["hidden_size"] // cfg["num_heads"]
+    x, t, y, pos, mask, target = synth.mixed_batch(cfg, shapes, 256, seed=11, rope_dim=d)
+    model = build_model(cfg, sd, precision)
+    with torch.no_grad():
+        out = model(x.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda(), train=True)
+    assert _valid_rel(out, z["out_train"], mask) < tol
+    h, w = shapes[0]
+    zz, tt, yy, pos_e, mask_e = synth.eval_batch(cfg, h, w, 256)
+    with torch.no_grad():
+        oc = model.forward_with_cfg(zz.cuda(), tt.cuda(), yy.cuda(), pos_e.cuda(), mask_e.cuda(), 1.5)
+    assert rel_l2(oc, z["out_cfg"]) < tol
+
+
+def test_padded_tokens_never_influence_valid_tokens():
+    """Size-independent property: garbage in the padded token slots changes no valid output bit."""
+    cfg = fo.model_config("FiT-B/2", depth=2)
+    sd = fo.random_state_dict(cfg, seed=3)
+    x, t, y, pos, mask, _ = synth.mixed_batch(cfg, [(20, 40), (16, 16), (32, 32)], 256, seed=5, rope_dim=64)
+    model = build_model(cfg, sd, "bf16")
+    with torch.no_grad():
+        a = model(x.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda()).cpu()
+        x2 = x.clone()
+        x2[~mask] = torch.randn_like(x2[~mask]) * 100
+        b = model(x2.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda()).cpu()
+    assert torch.equal(a[mask], b[mask])
+
+
+@pytest.mark.parametrize("precision,tol_final,tol_step", [("fp32", 1e-3, 1e-5), ("bf16", 5e-2, 1e-2)])
+def test_ten_step_sampling_matches_reference(precision, tol_final, tol_step):
+    """Fixed-seed 10-step DDPM / DDIM sampling with CFG 1.5 (config-1 shape scaled to the tiny model): final latents
+    within tol_final relative L2 of the reference trace (noise shared bit for bit), plus teacher-forced per-step
+    checks (random-weight sampling is chaotic: sqrt(1/abar_T) = 157)."""
+    from fit_b200.diffusion import create_diffusion
+    z = golden("sample_loop_tiny")
+    sd = fo.random_state_dict(TINY64, seed=7)
+    model = build_model(TINY64, sd, precision)
+    d = create_diffusion("10")
+    zz, yy = torch.tensor(z["z"]).cuda(), torch.tensor(z["y"]).cuda()
+    from oracle.pos_embed_oracle import precompute_freqs_cis_2d
+    pos = torch.tensor(precompute_freqs_cis_2d(64, 8, 8, max_length=64), dtype=torch.float32)[None].cuda()
+    mask = torch.ones(4, 64, dtype=torch.bool, device="cuda")
+    kw = dict(y=yy, pos=pos, mask=mask, cfg_scale=1.5)
+    noise = torch.tensor(z["noise"]).cuda()
+    trace = z["ddpm.trace"]
+    x = zz
+    with torch.no_grad():
+        for k, i in enumerate(reversed(range(10))):
+            t = torch.full((4,), i, dtype=torch.int64, device="cuda")
+            x = d.p_sample(model.forward_with_cfg, x, t, clip_denoised=False, model_kwargs=kw, noise=noise[k])["sample"]
+            # teacher-forced: one step from the reference's previous state
+            prev = zz if k == 0 else torch.tensor(trace[k - 1]).cuda()
+            tf = d.p_sample(model.forward_with_cfg, prev, t, clip_denoised=False, model_kwargs=kw, noise=noise[k])["sample"]
+            assert rel_l2(tf, trace[k]) < tol_step, f"step {k}"
+    assert rel_l2(x, trace[-1]) < tol_final
+    # DDIM loop through the public loop API (eta = 0: no noise drawn into the result)
+    with torch.no_grad():
+        xd = d.ddim_sample_loop(model.forward_with_cfg, zz.shape, zz, clip_denoised=False, model_kwargs=kw, device="cuda")
+    assert rel_l2(xd, z["ddim.final"]) < tol_final
+
+
+def test_graph_sampler_matches_python_loop_and_is_shard_invariant():
+    from fit_b200.diffusion import create_diffusion
+    from fit_b200.sampler import CFGSampler
+    from oracle.pos_embed_oracle import precompute_freqs_cis_2d
+    sd = fo.random_state_dict(TINY64, seed=7)
+    model = build_model(TINY64, sd, "bf16")
+    d = create_diffusion("10")
+    g = torch.Generator().manual_seed(2)
+    B = 6
+    zlat = torch.randn(B, 4, 16, 16, generator=g).cuda()
+    y = torch.randint(0, 10, (B,), generator=g).cuda()
+    pos = torch.tensor(precompute_freqs_cis_2d(64, 8, 8, max_length=64), dtype=torch.float32)[None].cuda()
+    s_all = CFGSampler(model, d, batch=B, latent_hw=(16, 16), cfg_scale=1.5, seed=77)
+    full = s_all.sample(zlat, y, pos)
+    # python loop with the sampler's own noise stream
+    x = torch.cat([zlat, zlat], 0)
+    yy = torch.cat([y, torch.full_like(y, 10)])
+    mask = torch.ones(2 * B, 64, dtype=torch.bool, device="cuda")
+    with torch.no_grad():
+        for i in reversed(range(10)):
+            t = torch.full((2 * B,), i, dtype=torch.int64, device="cuda")
+            nz = s_all.noise_for_step(i, row_offset=0, rows=B)
+            nz = torch.cat([nz, nz], 0)
+            x = d.p_sample(model.forward_with_cfg, x, t, clip_denoised=False, noise=nz,
+                           model_kwargs=dict(y=yy, pos=pos, mask=mask, cfg_scale=1.5))["sample"]
+    assert rel_l2(full, x[:B]) < 1e-5
+    # two shards of 3 images reproduce the 6-image run bit for bit (noise keyed by the global image index)
+    parts = []
+    for k in range(2):
+        s = CFGSampler(model, d, batch=3, latent_hw=(16, 16), cfg_scale=1.5, seed=77, row_offset=3 * k)
+        parts.append(s.sample(zlat[3 * k:3 * k + 3], y[3 * k:3 * k + 3], pos))
+    assert torch.equal(torch.cat(parts, 0), full)
+
+
+def test_no_fallback_without_cuda_tensors():
+    sd = fo.random_state_dict(TINY64, seed=7)
+    from fit_b200.models.fit import FiT
+    m = FiT(**TINY64)
+    m.load_state_dict(sd)
+    x, t, y, pos, mask, _ = synth.mixed_batch(TINY64, TINY_SHAPES, 64, seed=11, rope_dim=64)
+    with pytest.raises(RuntimeError):
+        with torch.no_grad():
+            m.eval()(x, t, y, pos, mask)
