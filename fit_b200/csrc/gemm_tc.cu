@@ -5,9 +5,12 @@
 //   * warp 0 : TMA producer   -- cp.async.bulk.tensor 128B-swizzled A/B k-slabs into a STAGES-deep ring
 //   * warp 1 : MMA issuer     -- one thread issues tcgen05.mma (M=128, N=BN, K=16) into TMEM,
 //                                tcgen05.commit releases smem slots / publishes the accumulator
-//   * warps 2-5 : epilogue    -- tcgen05.ld TMEM -> registers, fused bias / SiLU-gate / adaLN-gate +
-//                                residual, 16-byte global stores.  Two TMEM accumulator stages, so the
-//                                epilogue of tile i overlaps the mainloop of tile i+1.
+//   * warps 2-5 : epilogue    -- per 128-byte-wide output slab: tcgen05.ld TMEM -> registers, fused
+//                                bias / SiLU / SwiGLU / adaLN-gate + residual, 16-byte swizzled st.shared,
+//                                TMA store.  The residual slab is TMA-LOADED two slabs ahead, so the
+//                                epilogue issues no per-row global access at all (round-1 profile: the
+//                                row-per-thread global loads made the epilogue the bottleneck, long_scoreboard).
+//     Two TMEM accumulator stages: the epilogue of tile i overlaps the mainloop of tile i+1.
 // Every mbarrier wait is bounded (ptx::mbar_wait traps) so a pipeline bug cannot hang the device.
 #include <mutex>
 
@@ -19,70 +22,63 @@ namespace fitb200 {
 constexpr int GT_BM = 128, GT_BK = 64;
 constexpr int GT_THREADS = 192;  // producer + mma + 4 epilogue warps
 constexpr int GT_EPI_THREADS = 128;
+constexpr int GT_SLAB_BYTES = GT_BM * 128;  // 128 rows x 128 bytes
+constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - 256 /*barriers*/;
 
-template <int BN> struct GtCfg {
-  static constexpr int STAGES = BN == 256 ? 4 : (BN == 192 ? 5 : 6);
+template <int BN, int EPI> struct GtCfg {
   static constexpr int A_BYTES = GT_BM * GT_BK * 2;
   static constexpr int B_BYTES = BN * GT_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int EPI_BYTES = (EPI == FITB200_EPI_BIAS_GATE_RESID ? 4 : 2) * GT_SLAB_BYTES;  // out x2 (+ resid x2)
+  static constexpr int STAGES_RAW = (GT_SMEM_BUDGET - EPI_BYTES) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 6 ? 6 : STAGES_RAW;
   static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;  // 2 accumulator stages, power of two
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+  static_assert(STAGES >= 3, "pipeline too shallow");
 };
 
 struct GtParams {
   int M, N, K;
   const float* bias;
-  void* out; long ldo;
   const float* gate; long ld_gate; int rows_per_sample;
-  const void* resid; long ld_resid;
 };
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-  uint32_t lo[16], hi[16];
-  ptx::tmem_ld16(taddr, lo);
-  ptx::tmem_ld16(taddr + 16, hi);
-  ptx::tmem_ld_wait();
+__device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  ptx::tmem_ld16(taddr, r);
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { v[i] = __uint_as_float(lo[i]); v[16 + i] = __uint_as_float(hi[i]); }
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-template <typename T> __device__ __forceinline__ void store8(T* p, const float* v);
-template <> __device__ __forceinline__ void store8<float>(float* p, const float* v) {
-  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
-  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
-}
-template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float* v) {
-  uint4 o;
-  o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]); o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
-  *reinterpret_cast<uint4*>(p) = o;
-}
-template <typename T> __device__ __forceinline__ void load8(const T* p, float* v);
-template <> __device__ __forceinline__ void load8<float>(const float* p, float* v) {
-  float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-}
-template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float* v) {
-  Vec8<__nv_bfloat16> t = Vec8<__nv_bfloat16>::load(p);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) v[i] = t.v[i];
-}
-
-template <int BN, int EPI, typename OutT, typename ResT>
+// OutT = bf16: a slab is 64 output columns; OutT = float: 32 output columns (both 128 bytes per row).
+template <int BN, int EPI, typename OutT>
 __global__ void __launch_bounds__(GT_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GtParams p) {
-  using Cfg = GtCfg<BN>;
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GtParams p) {
+  using Cfg = GtCfg<BN, EPI>;
   constexpr int STAGES = Cfg::STAGES;
+  constexpr bool SWIGLU = EPI == FITB200_EPI_SWIGLU;
+  constexpr bool RESID = EPI == FITB200_EPI_BIAS_GATE_RESID;
+  constexpr int OUTC = 128 / (int)sizeof(OutT);       // output columns per slab
+  constexpr int ACCC = SWIGLU ? 2 * OUTC : OUTC;      // accumulator columns per slab
+  constexpr int NSLAB = BN / ACCC;
+  constexpr int CW = 16 / (int)sizeof(OutT);          // output columns per 16-byte chunk: 8 (bf16) or 4 (fp32)
+  static_assert(BN % ACCC == 0, "tile width must be a whole number of slabs");
+
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);  // SWIZZLE_128B needs 1024-byte alignment
   uint8_t* smemA = smem;
   uint8_t* smemB = smem + STAGES * Cfg::A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
-  uint64_t* full_bar = bars;                    // [STAGES]  TMA -> MMA
-  uint64_t* empty_bar = bars + STAGES;          // [STAGES]  MMA -> TMA
-  uint64_t* tfull_bar = bars + 2 * STAGES;      // [2]       MMA -> epilogue
-  uint64_t* tempty_bar = bars + 2 * STAGES + 2; // [2]       epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint8_t* smemOut = smem + STAGES * Cfg::STAGE_BYTES;          // [2][128 rows][128 B]
+  uint8_t* smemRes = smemOut + 2 * GT_SLAB_BYTES;               // [2][128 rows][128 B]  (RESID only)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
+  uint64_t* full_bar = bars;                     // [STAGES]  TMA -> MMA
+  uint64_t* empty_bar = bars + STAGES;           // [STAGES]  MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * STAGES;       // [2]       MMA -> epilogue
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       epilogue -> MMA
+  uint64_t* res_bar = bars + 2 * STAGES + 4;     // [2]       residual slab landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 6);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_n = ceil_div(p.N, BN), tiles_m = ceil_div(p.M, GT_BM);
@@ -92,8 +88,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (threadIdx.x == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
+    ptx::prefetch_tmap(&tmOut);
+    if (RESID) ptx::prefetch_tmap(&tmRes);
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
-    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull_bar[s], 1); ptx::mbar_init(&tempty_bar[s], GT_EPI_THREADS); }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull_bar[s], 1);
+      ptx::mbar_init(&tempty_bar[s], GT_EPI_THREADS);
+      ptx::mbar_init(&res_bar[s], 1);
+    }
     ptx::fence_mbar_init();
   }
   if (warp == 1) {  // one warp owns TMEM allocation and deallocation
@@ -152,64 +154,122 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else {
     // ------------------------------------------------------------------ epilogue warps (2..5)
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
-    const int row_in_tile = quarter * 32 + lane;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    const int row = quarter * 32 + lane;     // row inside the tile == TMEM lane
+    const bool leader = threadIdx.x == 64;   // first epilogue thread: issues the TMA stores / residual loads
+    const uint32_t sw = (uint32_t)(row & 7); // 128B-swizzle phase of this row
+    const int my_tiles = (int)blockIdx.x < num_tiles ? (num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    const int total_slabs = my_tiles * NSLAB;
+
+    // residual slab q (running index over this CTA's tiles) -> TMA load into resid buffer q & 1
+    auto issue_resid = [&](int qq) {
+      if (qq >= total_slabs) return;
+      const int tile = blockIdx.x + (qq / NSLAB) * gridDim.x, slab = qq % NSLAB;
+      const int rm0 = (tile / tiles_n) * GT_BM, rn0 = (tile % tiles_n) * BN + slab * OUTC;
+      ptx::mbar_arrive_expect_tx(&res_bar[qq & 1], GT_SLAB_BYTES);
+      ptx::tma_load_2d(smemRes + (qq & 1) * GT_SLAB_BYTES, &tmRes, &res_bar[qq & 1], rn0, rm0);
+    };
+    if (RESID && leader) { issue_resid(0); issue_resid(1); }
+
+    int q = 0;  // running slab index
+    for (int it = 0; it < my_tiles; ++it) {
+      const int tile = blockIdx.x + it * gridDim.x;
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       const int m0 = (tile / tiles_n) * GT_BM, n0 = (tile % tiles_n) * BN;
-      const int m = m0 + row_in_tile;
-      const bool row_ok = m < p.M;
+      const int m = min(m0 + row, p.M - 1);
+      const float* gate_row = nullptr;
+      if (RESID) gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
-      const float* gate_row = nullptr;
-      if (EPI == FITB200_EPI_BIAS_GATE_RESID && row_ok) gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        const int n = n0 + c * 32;
-        if (n >= p.N) break;  // warp-uniform
-        float acc[32];
-        __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the row-predicated stores below
-        tmem_ld32(taddr + c * 32, acc);
-        if (!row_ok) continue;
-        if (EPI == FITB200_EPI_SWIGLU) {
-          // packed weight: 16 gate rows then the matching 16 up rows -> 16 hidden units per chunk
-          const int j = n >> 1;
-          float o[16];
+      for (int slab = 0; slab < NSLAB; ++slab, ++q) {
+        const int buf = q & 1;
+        const int nacc = n0 + slab * ACCC;             // first accumulator column of the slab (global n)
+        const int nout = SWIGLU ? (nacc >> 1) : nacc;  // first output column
+        uint8_t* obuf = smemOut + buf * GT_SLAB_BYTES + row * 128;
+        const uint8_t* rbuf = smemRes + buf * GT_SLAB_BYTES + row * 128;
+        // the TMA store that read this staging buffer two slabs ago must have finished reading it
+        if (leader) ptx::tma_store_wait_read<1>();
+        if (RESID) ptx::mbar_wait(&res_bar[buf], (q >> 1) & 1);
+        ptx::named_bar_sync(1, GT_EPI_THREADS);
+        const bool live = nacc < p.N;  // tile-uniform: slabs beyond N are skipped (their store would be fully clipped)
+        if (live) {
+          float acc[ACCC];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float gv = acc[i] + __ldg(p.bias + n + i);
-            const float uv = acc[16 + i] + __ldg(p.bias + n + 16 + i);
-            o[i] = silu_f(gv) * uv;
-          }
-          OutT* op = (OutT*)p.out + (size_t)m * p.ldo + j;
-          store8<OutT>(op, o);
-          store8<OutT>(op + 8, o + 8);
-        } else {
+          for (int c = 0; c < ACCC / 16; ++c) tmem_ld16f(taddr + slab * ACCC + c * 16, acc + c * 16);
+          ptx::tmem_ld_wait();
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int nq = n + q * 8;
-            if (nq >= p.N) break;
+          for (int j = 0; j < 8; ++j) {  // 8 x 16-byte chunks per 128-byte row
             float v[8];
+            if (SWIGLU) {
+              // packed weight: every 32 accumulator columns = 16 gate rows then the matching 16 up rows
+              const int a0 = (j >> 1) * 32 + (j & 1) * 8;
+              const int nb = nacc + a0;
+              const bool ok = nb < p.N;
+              const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+              const float4 g0 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb)) : z4;
+              const float4 g1 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb + 4)) : z4;
+              const float4 u0 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb + 16)) : z4;
+              const float4 u1 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb + 20)) : z4;
+              const float bg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+              const float bu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = acc[q * 8 + i] + (p.bias ? __ldg(p.bias + nq + i) : 0.f);
-            if (EPI == FITB200_EPI_BIAS_SILU) {
+              for (int i = 0; i < 8; ++i) v[i] = silu_f(acc[a0 + i] + bg[i]) * (acc[a0 + 16 + i] + bu[i]);
+            } else {
+              const int nb = nacc + j * CW;
+              const bool ok = nb < p.N;
 #pragma unroll
-              for (int i = 0; i < 8; ++i) v[i] = silu_f(v[i]);
-            } else if (EPI == FITB200_EPI_BIAS_GATE_RESID) {
-              float r[8], gt[8];
-              load8<ResT>((const ResT*)p.resid + (size_t)m * p.ld_resid + nq, r);
-              load8<float>(gate_row + nq, gt);
+              for (int i4 = 0; i4 < CW / 4; ++i4) {
+                float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p.bias && ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + nb + i4 * 4));
+                v[i4 * 4 + 0] = acc[j * CW + i4 * 4 + 0] + b4.x; v[i4 * 4 + 1] = acc[j * CW + i4 * 4 + 1] + b4.y;
+                v[i4 * 4 + 2] = acc[j * CW + i4 * 4 + 2] + b4.z; v[i4 * 4 + 3] = acc[j * CW + i4 * 4 + 3] + b4.w;
+              }
+              if (EPI == FITB200_EPI_BIAS_SILU) {
 #pragma unroll
-              for (int i = 0; i < 8; ++i) v[i] = fmaf(gt[i], v[i], r[i]);
+                for (int i = 0; i < CW; ++i) v[i] = silu_f(v[i]);
+              } else if (RESID) {
+                const uint4 rraw = *reinterpret_cast<const uint4*>(rbuf + ((j ^ sw) << 4));
+                float r[8];
+                if constexpr (sizeof(OutT) == 2) {
+                  const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&rraw);
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h2[i]); r[2 * i] = f.x; r[2 * i + 1] = f.y; }
+                } else {
+                  r[0] = __uint_as_float(rraw.x); r[1] = __uint_as_float(rraw.y); r[2] = __uint_as_float(rraw.z); r[3] = __uint_as_float(rraw.w);
+                }
+#pragma unroll
+                for (int i4 = 0; i4 < CW / 4; ++i4) {
+                  float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                  if (ok) g4 = __ldg(reinterpret_cast<const float4*>(gate_row + nb + i4 * 4));
+                  v[i4 * 4 + 0] = fmaf(g4.x, v[i4 * 4 + 0], r[i4 * 4 + 0]); v[i4 * 4 + 1] = fmaf(g4.y, v[i4 * 4 + 1], r[i4 * 4 + 1]);
+                  v[i4 * 4 + 2] = fmaf(g4.z, v[i4 * 4 + 2], r[i4 * 4 + 2]); v[i4 * 4 + 3] = fmaf(g4.w, v[i4 * 4 + 3], r[i4 * 4 + 3]);
+                }
+              }
             }
-            store8<OutT>((OutT*)p.out + (size_t)m * p.ldo + nq, v);
+            uint4 o;
+            if constexpr (sizeof(OutT) == 2) {
+              o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]); o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+            } else {
+              o.x = __float_as_uint(v[0]); o.y = __float_as_uint(v[1]); o.z = __float_as_uint(v[2]); o.w = __float_as_uint(v[3]);
+            }
+            *reinterpret_cast<uint4*>(obuf + ((j ^ sw) << 4)) = o;
           }
         }
+        if (slab == NSLAB - 1) {  // accumulator fully read: hand the TMEM stage back to the MMA warp
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(&tempty_bar[as]);
+        }
+        ptx::fence_proxy_async_smem();  // make the st.shared visible to the TMA (async proxy)
+        ptx::named_bar_sync(1, GT_EPI_THREADS);
+        if (leader) {
+          if (live) ptx::tma_store_2d(&tmOut, smemOut + buf * GT_SLAB_BYTES, nout, m0);
+          ptx::tma_store_commit();
+          if (RESID) issue_resid(q + 2);  // this residual buffer has been consumed by all 128 threads
+        }
       }
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(&tempty_bar[as]);
     }
+    if (leader) ptx::tma_store_wait_all();
   }
 
   ptx::tc_fence_before();
@@ -238,33 +298,44 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
-// 2-D bf16 row-major [rows, cols] with leading dimension ld (elements); box = box_rows x 64 columns, 128B swizzle
-static int make_tmap(CUtensorMap* m, const void* ptr, long rows, long cols, long ld, int box_rows) {
+// 2-D row-major [rows, cols] tensor with leading dimension ld (elements); box = box_rows x box_cols, 128B swizzle
+// (box_cols * element bytes must be 128)
+static int make_tmap(CUtensorMap* m, const void* ptr, int dtype, long rows, long cols, long ld, int box_rows, int box_cols) {
   EncodeTiledFn enc = get_encode();
   if (!enc) { set_last_error("gemm_bf16_tc: cuTensorMapEncodeTiled not available from the driver"); return FITB200_ERR_CUDA; }
+  const int eb = dtype == FITB200_BF16 ? 2 : 4;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {(cuuint32_t)GT_BK, (cuuint32_t)box_rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * eb};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(m, dtype == FITB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                   const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_last_error("gemm_bf16_tc: cuTensorMapEncodeTiled failed (%d) rows=%ld cols=%ld ld=%ld", (int)r, rows, cols, ld); return FITB200_ERR_CUDA; }
   return FITB200_OK;
 }
 
-template <int BN, int EPI, typename OutT, typename ResT>
+template <int BN, int EPI, typename OutT>
 static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
-  using Cfg = GtCfg<BN>;
-  CUtensorMap tmA, tmB;
-  int rc = make_tmap(&tmA, a.A, a.M, a.K, a.lda, GT_BM);
+  using Cfg = GtCfg<BN, EPI>;
+  CUtensorMap tmA, tmB, tmOut, tmRes;
+  int rc = make_tmap(&tmA, a.A, FITB200_BF16, a.M, a.K, a.lda, GT_BM, GT_BK);
   if (rc) return rc;
-  rc = make_tmap(&tmB, a.B, a.N, a.K, a.ldb, BN);
+  rc = make_tmap(&tmB, a.B, FITB200_BF16, a.N, a.K, a.ldb, BN, GT_BK);
   if (rc) return rc;
+  const int outc = 128 / (int)sizeof(OutT);
+  const long n_out = EPI == FITB200_EPI_SWIGLU ? a.N / 2 : a.N;
+  rc = make_tmap(&tmOut, a.out, a.out_dtype, a.M, n_out, a.ldo, GT_BM, outc);
+  if (rc) return rc;
+  tmRes = tmOut;
+  if (EPI == FITB200_EPI_BIAS_GATE_RESID) {
+    rc = make_tmap(&tmRes, a.resid, a.out_dtype, a.M, a.N, a.ld_resid, GT_BM, outc);
+    if (rc) return rc;
+  }
   GtParams p;
-  p.M = a.M; p.N = a.N; p.K = a.K; p.bias = a.bias; p.out = a.out; p.ldo = a.ldo;
-  p.gate = a.gate; p.ld_gate = a.ld_gate; p.rows_per_sample = a.rows_per_sample; p.resid = a.resid; p.ld_resid = a.ld_resid;
-  auto kern = gemm_tc_kernel<BN, EPI, OutT, ResT>;
+  p.M = a.M; p.N = a.N; p.K = a.K; p.bias = a.bias;
+  p.gate = a.gate; p.ld_gate = a.ld_gate; p.rows_per_sample = a.rows_per_sample;
+  auto kern = gemm_tc_kernel<BN, EPI, OutT>;
   static bool attr_done = false;  // per template instantiation
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -273,7 +344,7 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   }
   const int tiles = ceil_div(a.M, GT_BM) * ceil_div(a.N, BN);
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  kern<<<grid, GT_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, p);
+  kern<<<grid, GT_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmOut, tmRes, p);
   FITB200_CHECK_LAUNCH("gemm_bf16_tc");
   return FITB200_OK;
 }
@@ -281,15 +352,14 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
 template <int BN, typename OutT>
 static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
   switch (a.epilogue) {
-    case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT, float>(a, s);
-    case FITB200_EPI_BIAS_SILU: return launch_tc<BN, FITB200_EPI_BIAS_SILU, OutT, float>(a, s);
-    case FITB200_EPI_SWIGLU: return launch_tc<BN, FITB200_EPI_SWIGLU, OutT, float>(a, s);
-    case FITB200_EPI_BIAS_GATE_RESID:
-      if (a.resid_dtype == FITB200_F32) return launch_tc<BN, FITB200_EPI_BIAS_GATE_RESID, OutT, float>(a, s);
-      if (a.resid_dtype == FITB200_BF16) return launch_tc<BN, FITB200_EPI_BIAS_GATE_RESID, OutT, __nv_bfloat16>(a, s);
+    case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT>(a, s);
+    case FITB200_EPI_BIAS_SILU: return launch_tc<BN, FITB200_EPI_BIAS_SILU, OutT>(a, s);
+    case FITB200_EPI_SWIGLU:
+      if constexpr (BN != 192) return launch_tc<BN, FITB200_EPI_SWIGLU, OutT>(a, s);  // 128 accumulator columns per slab
       break;
+    case FITB200_EPI_BIAS_GATE_RESID: return launch_tc<BN, FITB200_EPI_BIAS_GATE_RESID, OutT>(a, s);
   }
-  set_last_error("gemm_bf16_tc: unsupported epilogue %d / resid dtype %d", a.epilogue, a.resid_dtype);
+  set_last_error("gemm_bf16_tc: unsupported epilogue %d", a.epilogue);
   return FITB200_ERR_INVALID_ARG;
 }
 
@@ -299,6 +369,7 @@ static int dispatch_bn(const fitb200_gemm_args& a, cudaStream_t s) {
   int best = 256; long best_waste = (long)ceil_div(a.N, 256) * 256 - a.N;
   const int cand[2] = {192, 128};
   for (int c : cand) {
+    if (c == 192 && a.epilogue == FITB200_EPI_SWIGLU) continue;
     long w = (long)ceil_div(a.N, c) * c - a.N;
     if (w < best_waste) { best = c; best_waste = w; }
   }
@@ -318,11 +389,12 @@ extern "C" int fitb200_gemm_bf16_tc(const fitb200_gemm_args* ap, fitb200_stream_
   FITB200_CHECK_ARG(a.K % 8 == 0 && a.lda % 8 == 0 && a.ldb % 8 == 0, "gemm_bf16_tc: K, lda, ldb must be multiples of 8 (K=%d lda=%lld ldb=%lld)", a.K, (long long)a.lda, (long long)a.ldb);
   FITB200_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.B & 15) == 0 && ((uintptr_t)a.out & 15) == 0, "gemm_bf16_tc: A, B, out must be 16-byte aligned");
   FITB200_CHECK_ARG(a.N % 8 == 0 && a.ldo % 8 == 0, "gemm_bf16_tc: N and ldo must be multiples of 8 (N=%d)", a.N);
+  FITB200_CHECK_ARG(a.bias == nullptr || ((uintptr_t)a.bias & 15) == 0, "gemm_bf16_tc: bias must be 16-byte aligned");
   if (a.epilogue == FITB200_EPI_SWIGLU) FITB200_CHECK_ARG(a.N % 32 == 0 && a.bias, "gemm_bf16_tc: SWIGLU needs N %% 32 == 0 and a packed bias");
   if (a.epilogue == FITB200_EPI_BIAS_GATE_RESID)
     FITB200_CHECK_ARG(a.gate && a.resid && a.rows_per_sample > 0 && a.ld_gate % 4 == 0 && a.ld_resid % 8 == 0 &&
-                          ((uintptr_t)a.gate & 15) == 0 && ((uintptr_t)a.resid & 15) == 0,
-                      "gemm_bf16_tc: GATE_RESID needs aligned gate/resid and rows_per_sample");
+                          ((uintptr_t)a.gate & 15) == 0 && ((uintptr_t)a.resid & 15) == 0 && a.resid_dtype == a.out_dtype,
+                      "gemm_bf16_tc: GATE_RESID needs 16-byte aligned gate/resid, rows_per_sample, and resid dtype == out dtype");
   if (a.out_dtype == FITB200_BF16) return dispatch_bn<__nv_bfloat16>(a, (cudaStream_t)stream);
   if (a.out_dtype == FITB200_F32) return dispatch_bn<float>(a, (cudaStream_t)stream);
   set_last_error("gemm_bf16_tc: unsupported out dtype %d", a.out_dtype);
