@@ -13,6 +13,7 @@ and "fp32" (verification mode: CUDA-core fp32 GEMMs and fp32 activations).
 """
 from __future__ import annotations
 
+import math
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -48,6 +49,10 @@ class _Weights:
         self.t0_w, self.t0_b = f32(model.t_embedder.mlp[0].weight), f32(model.t_embedder.mlp[0].bias)
         self.t2_w, self.t2_b = f32(model.t_embedder.mlp[2].weight), f32(model.t_embedder.mlp[2].bias)
         self.y_table = f32(model.y_embedder.embedding_table.weight)
+        # fit.py:73-75: the sinusoid frequencies are a host-side fp32 table in the reference; computing them the
+        # same way (CPU torch.exp) keeps the arguments t*f bit-identical to the reference's
+        half = 128
+        self.t_freqs = torch.exp(-math.log(10000.0) * torch.arange(half, dtype=torch.float32) / half).to(self.y_table.device)
         # adaLN of every block and of the final layer as ONE [L*6D + 2D, D] weight: c is shared by all of
         # them (fit.py:505,513; dit.py:139), so a single small-M GEMM per forward produces the whole table
         ada_w = [b.adaLN_modulation[1].weight for b in model.blocks] + [model.final_layer.adaLN_modulation[1].weight]
@@ -154,7 +159,7 @@ class FiTEngine:
     # ------------------------------------------------------------------ pieces
     def conditioning(self, ws: _Workspace, W: _Weights, t: Tensor, y: Tensor):
         """t_embedder + y_embedder + c = t + y (fit.py:503-505) and the adaLN table of all blocks."""
-        ops.timestep_sincos(t, ws.tfreq)
+        ops.timestep_sincos(t, ws.tfreq, W.t_freqs)
         ops.gemm(ws.tfreq, W.t0_w, W.t0_b, ws.t1, EPI_BIAS_SILU)
         ops.gemm(ws.t1, W.t2_w, W.t2_b, ws.t2, EPI_BIAS)
         ops.cond_combine(ws.t2, y, W.y_table, ws.c, ws.silu_c)

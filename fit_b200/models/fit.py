@@ -71,7 +71,8 @@ class TimestepEmbedder(nn.Module):
 
     def forward(self, t: Tensor) -> Tensor:
         f = torch.empty(t.shape[0], 256, dtype=torch.float32, device=t.device)
-        ops.timestep_sincos(t.to(torch.int64), f)
+        freqs = torch.exp(-math.log(10000.0) * torch.arange(128, dtype=torch.float32) / 128).to(t.device)  # fit.py:73-75
+        ops.timestep_sincos(t.to(torch.int64), f, freqs)
         return self.mlp[2](self.mlp[0](f, EPI_BIAS_SILU))
 
 
