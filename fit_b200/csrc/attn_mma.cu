@@ -9,7 +9,10 @@ namespace fitb200 {
 int attn_fwd_f32(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask,
                  int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s);
 
-constexpr int AM_BQ = 64, AM_BK = 64, AM_THREADS = 128;
+constexpr int AM_BQ = 128;      // queries per CTA: 8 warps x 16 rows
+constexpr int AM_BK = 64;       // keys per softmax tile
+constexpr int AM_CHUNK = 256;   // keys resident in shared memory at a time (the whole sequence when T <= 256)
+constexpr int AM_THREADS = 256;
 
 __device__ __forceinline__ void ldsm_x4(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, const void* p) {
   uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
@@ -29,11 +32,14 @@ __device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], 
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(a), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory"); }
 
-// load 8 consecutive bf16 of a q/k row, rotate the 4 (re, im) pairs by the fp32 table, round to bf16
-__device__ __forceinline__ uint4 load_rotate8(const __nv_bfloat16* p, const float* f) {
-  uint4 raw = *reinterpret_cast<const uint4*>(p);
-  float4 f0 = *reinterpret_cast<const float4*>(f), f1 = *reinterpret_cast<const float4*>(f + 4);
+// rotate the 4 (re, im) pairs of 8 consecutive bf16 by the fp32 (cos, sin) table, round to bf16 (complex_mult, fit.py:152-154)
+__device__ __forceinline__ uint4 rotate8(const uint4 raw, const float4 f0, const float4 f1) {
   const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&raw);
   const float cs[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
   uint4 o;
@@ -42,27 +48,63 @@ __device__ __forceinline__ uint4 load_rotate8(const __nv_bfloat16* p, const floa
   for (int i = 0; i < 4; ++i) {
     float2 ab = __bfloat1622float2(h2[i]);
     float c = cs[2 * i], s = cs[2 * i + 1];
-    ow[i] = pack_bf16x2(ab.x * c - ab.y * s, ab.y * c + ab.x * s);  // complex_mult, fit.py:152-154
+    ow[i] = pack_bf16x2(ab.x * c - ab.y * s, ab.y * c + ab.x * s);
   }
   return o;
 }
 
+// Load `nrows` rows (HD bf16 each, global row stride `gstride` elements) starting at token t0, rotate them by the RoPE
+// table and store them as smem rows of LDS elements; rows in [nvalid, nrows) and the pad columns [HD, LDS) are zeroed.
+// Loads are issued UNR at a time so each thread keeps UNR x 48 bytes in flight.
+template <int HD, int LDS>
+__device__ __forceinline__ void load_rotate_rows(__nv_bfloat16* dst, const __nv_bfloat16* __restrict__ src, size_t gstride,
+                                                 const float* __restrict__ fr, int t0, int nrows, int nvalid, int tid) {
+  constexpr int CH = HD / 8, CHP = LDS / 8, UNR = 2;
+  const int total = nrows * CHP;
+  for (int i0 = tid; i0 < total; i0 += AM_THREADS * UNR) {
+    uint4 raw[UNR]; float4 f0[UNR], f1[UNR]; bool live[UNR];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const int i = i0 + u * AM_THREADS;
+      const int row = i / CHP, c = i - row * CHP;
+      live[u] = i < total && c < CH && row < nvalid;
+      if (live[u]) {
+        const size_t t = (size_t)(t0 + row);
+        raw[u] = *reinterpret_cast<const uint4*>(src + t * gstride + c * 8);
+        f0[u] = __ldg(reinterpret_cast<const float4*>(fr + t * HD + c * 8));
+        f1[u] = __ldg(reinterpret_cast<const float4*>(fr + t * HD + c * 8 + 4));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const int i = i0 + u * AM_THREADS;
+      if (i < total) {
+        const int row = i / CHP, c = i - row * CHP;
+        *reinterpret_cast<uint4*>(dst + row * LDS + c * 8) = live[u] ? rotate8(raw[u], f0[u], f1[u]) : make_uint4(0, 0, 0, 0);
+      }
+    }
+  }
+}
+
+// One CTA = 128 queries of one (sample, head).  The keys/values of the sample are staged in shared memory in chunks of
+// 256 (one chunk when T <= 256): K rotated in registers on the way in, V by cp.async.  Each warp owns 16 query rows
+// (Q fragments live in registers) and runs the online softmax over 64-key tiles of the resident chunk.
 template <int HD>
-__global__ void __launch_bounds__(AM_THREADS) attn_mma_kernel(const __nv_bfloat16* __restrict__ qkv,
-                                                              const float* __restrict__ freqs, int freqs_rows,
-                                                              const int32_t* __restrict__ kv_len,
-                                                              const uint8_t* __restrict__ mask, int R, int Tn, int h,
-                                                              __nv_bfloat16* __restrict__ out, float* __restrict__ lse) {
-  constexpr int HDP = (HD + 15) / 16 * 16;  // contraction width of q.k^T (72 -> 80)
-  constexpr int LDS = HDP + 8;              // smem row stride in elements (conflict-free ldmatrix)
+__global__ void __launch_bounds__(AM_THREADS, 2) attn_mma_kernel(const __nv_bfloat16* __restrict__ qkv,
+                                                                 const float* __restrict__ freqs, int freqs_rows,
+                                                                 const int32_t* __restrict__ kv_len,
+                                                                 const uint8_t* __restrict__ mask, int R, int Tn, int h,
+                                                                 __nv_bfloat16* __restrict__ out, float* __restrict__ lse) {
+  constexpr int HDP = (HD + 15) / 16 * 16;  // contraction width of q.k^T (72 -> 80, zero padded)
+  constexpr int LDS = HDP + 8;              // smem row stride in elements: odd multiple of 16 bytes => conflict-free ldmatrix
   constexpr int KSTEPS = HDP / 16;
   constexpr int NT_O = HD / 8;              // output n-tiles
   constexpr int CH = HD / 8;                // 16-byte chunks per row
 
-  __shared__ __align__(16) __nv_bfloat16 Qs[AM_BQ * LDS];
-  __shared__ __align__(16) __nv_bfloat16 Ks[AM_BK * LDS];
-  __shared__ __align__(16) __nv_bfloat16 Vs[AM_BK * LDS];
-  __shared__ uint8_t kvalid[AM_BK];
+  extern __shared__ __align__(16) uint8_t attn_smem[];
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(attn_smem);  // [AM_CHUNK][LDS]
+  __nv_bfloat16* Vs = Ks + AM_CHUNK * LDS;                          // [AM_CHUNK][LDS]; first the Q tile, last the output staging
+  uint8_t* kvalid = reinterpret_cast<uint8_t*>(Vs + AM_CHUNK * LDS);  // [AM_CHUNK]
 
   const int r = blockIdx.z, head = blockIdx.y, q0 = blockIdx.x * AM_BQ;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -83,21 +125,13 @@ __global__ void __launch_bounds__(AM_THREADS) attn_mma_kernel(const __nv_bfloat1
     return;
   }
 
-  // ---- Q tile: HBM -> rotate in registers -> smem
-  for (int i = tid; i < AM_BQ * (LDS / 8); i += AM_THREADS) {
-    int row = i / (LDS / 8), c = i - row * (LDS / 8);
-    uint4 v = make_uint4(0, 0, 0, 0);
-    int t = q0 + row;
-    if (c < CH && t < Tn) v = load_rotate8(base + (size_t)t * row_stride + c * 8, fr + (size_t)t * HD + c * 8);
-    *reinterpret_cast<uint4*>(Qs + row * LDS + c * 8) = v;
-  }
+  // ---- Q tile: HBM -> rotate in registers -> smem (V region) -> A fragments in registers for the whole kernel
+  load_rotate_rows<HD, LDS>(Vs, base, row_stride, fr, q0, AM_BQ, min(AM_BQ, Tn - q0), tid);
   __syncthreads();
-
-  // Q A-fragments stay in registers for the whole kernel
   uint32_t qf[KSTEPS][4];
 #pragma unroll
   for (int ks = 0; ks < KSTEPS; ++ks) {
-    const __nv_bfloat16* p = Qs + (warp * 16 + (lane & 15)) * LDS + ks * 16 + (lane >> 4) * 8;
+    const __nv_bfloat16* p = Vs + (warp * 16 + (lane & 15)) * LDS + ks * 16 + (lane >> 4) * 8;
     ldsm_x4(qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], p);
   }
 
@@ -107,103 +141,108 @@ __global__ void __launch_bounds__(AM_THREADS) attn_mma_kernel(const __nv_bfloat1
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
   const float sl2 = rsqrtf((float)HD) * 1.4426950408889634f;  // softmax scale folded with log2(e)
 
-  for (int k0 = 0; k0 < kvl; k0 += AM_BK) {
-    __syncthreads();  // previous tile fully consumed
-    for (int i = tid; i < AM_BK * (LDS / 8); i += AM_THREADS) {
-      int row = i / (LDS / 8), c = i - row * (LDS / 8);
-      uint4 kv4 = make_uint4(0, 0, 0, 0), vv4 = make_uint4(0, 0, 0, 0);
-      int t = k0 + row;
-      if (c < CH && t < kvl) {
-        const __nv_bfloat16* kp = base + (size_t)t * row_stride + (size_t)D + c * 8;
-        kv4 = load_rotate8(kp, fr + (size_t)t * HD + c * 8);
-        vv4 = *reinterpret_cast<const uint4*>(kp + D);
-      }
-      *reinterpret_cast<uint4*>(Ks + row * LDS + c * 8) = kv4;
-      *reinterpret_cast<uint4*>(Vs + row * LDS + c * 8) = vv4;
+  for (int c0 = 0; c0 < kvl; c0 += AM_CHUNK) {
+    __syncthreads();  // Q fragments read / previous chunk fully consumed: the smem regions may be overwritten
+    const int nk = min(AM_CHUNK, kvl - c0);
+    const int ntiles = ceil_div(nk, AM_BK);
+    const int nrows = ntiles * AM_BK;
+    // V: asynchronous 16-byte copies (no transform); rows in [nk, nrows) zeroed so that 0 * garbage cannot make NaN
+    for (int i = tid; i < nrows * CH; i += AM_THREADS) {
+      const int row = i / CH, c = i - row * CH;
+      __nv_bfloat16* dst = Vs + row * LDS + c * 8;
+      if (row < nk) cp_async16(dst, base + (size_t)(c0 + row) * row_stride + 2 * (size_t)D + c * 8);
+      else *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
     }
-    if (tid < AM_BK) {
-      int t = k0 + tid;
-      kvalid[tid] = (t < kvl) && (mask == nullptr || mask[(size_t)r * Tn + t] != 0);
-    }
+    // K: rotate in registers on the way to shared memory
+    load_rotate_rows<HD, LDS>(Ks, base + D, row_stride, fr, c0, nrows, nk, tid);
+    for (int j = tid; j < nrows; j += AM_THREADS)
+      kvalid[j] = (j < nk) && (mask == nullptr || mask[(size_t)r * Tn + c0 + j] != 0);
+    cp_async_wait_all();
     __syncthreads();
 
-    // ---- S = Q K^T  (16 x 64 per warp)
-    float s[AM_BK / 8][4];
+    for (int kt = 0; kt < ntiles; ++kt) {
+      const __nv_bfloat16* Kt = Ks + kt * AM_BK * LDS;
+      const __nv_bfloat16* Vt = Vs + kt * AM_BK * LDS;
+      const uint8_t* kval = kvalid + kt * AM_BK;
+      // ---- S = Q K^T  (16 x 64 per warp)
+      float s[AM_BK / 8][4];
 #pragma unroll
-    for (int n = 0; n < AM_BK / 8; ++n) { s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f; }
+      for (int n = 0; n < AM_BK / 8; ++n) { s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f; }
 #pragma unroll
-    for (int ks = 0; ks < KSTEPS; ++ks) {
+      for (int ks = 0; ks < KSTEPS; ++ks) {
 #pragma unroll
-      for (int np = 0; np < AM_BK / 16; ++np) {
-        // two key n-tiles (8 keys each) x 16 contraction columns in one ldmatrix.x4
-        uint32_t b0, b1, b2, b3;
-        const __nv_bfloat16* p = Ks + (np * 16 + (lane & 7) + ((lane >> 4) << 3)) * LDS + ks * 16 + ((lane >> 3) & 1) * 8;
-        ldsm_x4(b0, b1, b2, b3, p);
-        mma_bf16(s[2 * np], qf[ks], b0, b1);
-        mma_bf16(s[2 * np + 1], qf[ks], b2, b3);
+        for (int np = 0; np < AM_BK / 16; ++np) {
+          // two key n-tiles (8 keys each) x 16 contraction columns in one ldmatrix.x4
+          uint32_t b0, b1, b2, b3;
+          const __nv_bfloat16* p = Kt + (np * 16 + (lane & 7) + ((lane >> 4) << 3)) * LDS + ks * 16 + ((lane >> 3) & 1) * 8;
+          ldsm_x4(b0, b1, b2, b3, p);
+          mma_bf16(s[2 * np], qf[ks], b0, b1);
+          mma_bf16(s[2 * np + 1], qf[ks], b2, b3);
+        }
       }
-    }
 
-    // ---- mask + online softmax (rows g and g+8 of this warp's 16)
-    float mx0 = -INFINITY, mx1 = -INFINITY;
+      // ---- mask + online softmax (rows g and g+8 of this warp's 16)
+      float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-    for (int n = 0; n < AM_BK / 8; ++n) {
-      const int c = n * 8 + tq4 * 2;
-      const bool v0 = kvalid[c], v1 = kvalid[c + 1];
-      s[n][0] = v0 ? s[n][0] * sl2 : -INFINITY;
-      s[n][1] = v1 ? s[n][1] * sl2 : -INFINITY;
-      s[n][2] = v0 ? s[n][2] * sl2 : -INFINITY;
-      s[n][3] = v1 ? s[n][3] * sl2 : -INFINITY;
-      mx0 = fmaxf(mx0, fmaxf(s[n][0], s[n][1]));
-      mx1 = fmaxf(mx1, fmaxf(s[n][2], s[n][3]));
-    }
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-    // all keys of the tile masked -> mn = -inf: keep everything at zero without producing NaN
-    const float ms0 = mn0 == -INFINITY ? 0.f : mn0, ms1 = mn1 == -INFINITY ? 0.f : mn1;
-    const float c0 = exp2f(m0 - ms0), c1 = exp2f(m1 - ms1);
-    m0 = mn0; m1 = mn1;
-    float rs0 = 0.f, rs1 = 0.f;
-    uint32_t pf[AM_BK / 8][2];
-#pragma unroll
-    for (int n = 0; n < AM_BK / 8; ++n) {
-      float p0 = exp2f(s[n][0] - ms0), p1 = exp2f(s[n][1] - ms0);
-      float p2 = exp2f(s[n][2] - ms1), p3 = exp2f(s[n][3] - ms1);
-      rs0 += p0 + p1; rs1 += p2 + p3;
-      pf[n][0] = pack_bf16x2(p0, p1);
-      pf[n][1] = pack_bf16x2(p2, p3);
-    }
-    l0 = l0 * c0 + rs0; l1 = l1 * c1 + rs1;
-#pragma unroll
-    for (int n = 0; n < NT_O; ++n) { o[n][0] *= c0; o[n][1] *= c0; o[n][2] *= c1; o[n][3] *= c1; }
-
-    // ---- O += P V
-#pragma unroll
-    for (int kk = 0; kk < AM_BK / 16; ++kk) {
-      const uint32_t a[4] = {pf[2 * kk][0], pf[2 * kk][1], pf[2 * kk + 1][0], pf[2 * kk + 1][1]};
-#pragma unroll
-      for (int np = 0; np < NT_O / 2; ++np) {
-        uint32_t b0, b1, b2, b3;
-        const __nv_bfloat16* p = Vs + (kk * 16 + (lane & 15)) * LDS + np * 16 + (lane >> 4) * 8;
-        ldsm_x4_t(b0, b1, b2, b3, p);
-        mma_bf16(o[2 * np], a, b0, b1);
-        mma_bf16(o[2 * np + 1], a, b2, b3);
+      for (int n = 0; n < AM_BK / 8; ++n) {
+        const int c = n * 8 + tq4 * 2;
+        const bool v0 = kval[c], v1 = kval[c + 1];
+        s[n][0] = v0 ? s[n][0] * sl2 : -INFINITY;
+        s[n][1] = v1 ? s[n][1] * sl2 : -INFINITY;
+        s[n][2] = v0 ? s[n][2] * sl2 : -INFINITY;
+        s[n][3] = v1 ? s[n][3] * sl2 : -INFINITY;
+        mx0 = fmaxf(mx0, fmaxf(s[n][0], s[n][1]));
+        mx1 = fmaxf(mx1, fmaxf(s[n][2], s[n][3]));
       }
-      if (NT_O & 1) {
-        uint32_t b0, b1;
-        const __nv_bfloat16* p = Vs + (kk * 16 + (lane & 15)) * LDS + (NT_O - 1) * 8;
-        ldsm_x2_t(b0, b1, p);
-        mma_bf16(o[NT_O - 1], a, b0, b1);
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+      // all keys so far masked -> mn = -inf: keep everything at zero without producing NaN
+      const float ms0 = mn0 == -INFINITY ? 0.f : mn0, ms1 = mn1 == -INFINITY ? 0.f : mn1;
+      const float c0s = exp2f(m0 - ms0), c1s = exp2f(m1 - ms1);
+      m0 = mn0; m1 = mn1;
+      float rs0 = 0.f, rs1 = 0.f;
+      uint32_t pf[AM_BK / 8][2];
+#pragma unroll
+      for (int n = 0; n < AM_BK / 8; ++n) {
+        float p0 = exp2f(s[n][0] - ms0), p1 = exp2f(s[n][1] - ms0);
+        float p2 = exp2f(s[n][2] - ms1), p3 = exp2f(s[n][3] - ms1);
+        rs0 += p0 + p1; rs1 += p2 + p3;
+        pf[n][0] = pack_bf16x2(p0, p1);
+        pf[n][1] = pack_bf16x2(p2, p3);
+      }
+      l0 = l0 * c0s + rs0; l1 = l1 * c1s + rs1;
+#pragma unroll
+      for (int n = 0; n < NT_O; ++n) { o[n][0] *= c0s; o[n][1] *= c0s; o[n][2] *= c1s; o[n][3] *= c1s; }
+
+      // ---- O += P V
+#pragma unroll
+      for (int kk = 0; kk < AM_BK / 16; ++kk) {
+        const uint32_t a[4] = {pf[2 * kk][0], pf[2 * kk][1], pf[2 * kk + 1][0], pf[2 * kk + 1][1]};
+#pragma unroll
+        for (int np = 0; np < NT_O / 2; ++np) {
+          uint32_t b0, b1, b2, b3;
+          const __nv_bfloat16* p = Vt + (kk * 16 + (lane & 15)) * LDS + np * 16 + (lane >> 4) * 8;
+          ldsm_x4_t(b0, b1, b2, b3, p);
+          mma_bf16(o[2 * np], a, b0, b1);
+          mma_bf16(o[2 * np + 1], a, b2, b3);
+        }
+        if (NT_O & 1) {
+          uint32_t b0, b1;
+          const __nv_bfloat16* p = Vt + (kk * 16 + (lane & 15)) * LDS + (NT_O - 1) * 8;
+          ldsm_x2_t(b0, b1, p);
+          mma_bf16(o[NT_O - 1], a, b0, b1);
+        }
       }
     }
   }
 
-  // ---- finalise: row sums across the quad, normalise, stage through this warp's Q rows, 16-byte stores
+  // ---- finalise: row sums across the quad, normalise, stage through this warp's slice of the V region, 16-byte stores
   l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
   l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
   const float i0 = l0 > 0.f ? 1.f / l0 : 0.f, i1 = l1 > 0.f ? 1.f / l1 : 0.f;
-  __nv_bfloat16* stage = Qs + warp * 16 * LDS;
+  __syncthreads();  // every warp is done reading K / V
+  __nv_bfloat16* stage = Vs + warp * 16 * LDS;
 #pragma unroll
   for (int n = 0; n < NT_O; ++n) {
     *reinterpret_cast<uint32_t*>(stage + g * LDS + n * 8 + tq4 * 2) = pack_bf16x2(o[n][0] * i0, o[n][1] * i0);
@@ -228,9 +267,17 @@ __global__ void __launch_bounds__(AM_THREADS) attn_mma_kernel(const __nv_bfloat1
 template <int HD>
 static int launch_attn_mma(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len,
                            const uint8_t* mask, int R, int Tn, int h, void* out, float* lse, cudaStream_t s) {
+  constexpr int LDS = (HD + 15) / 16 * 16 + 8;
+  constexpr int SMEM = 2 * AM_CHUNK * LDS * 2 + AM_CHUNK;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(attn_mma_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) { set_last_error("attn_mma: cannot set %d bytes of dynamic smem: %s", SMEM, cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
+    attr_done = true;
+  }
   dim3 grid((unsigned)ceil_div(Tn, AM_BQ), (unsigned)h, (unsigned)R);
-  attn_mma_kernel<HD><<<grid, AM_THREADS, 0, s>>>((const __nv_bfloat16*)qkv, freqs, freqs_rows, kv_len, mask, R, Tn, h,
-                                                  (__nv_bfloat16*)out, lse);
+  attn_mma_kernel<HD><<<grid, AM_THREADS, SMEM, s>>>((const __nv_bfloat16*)qkv, freqs, freqs_rows, kv_len, mask, R, Tn, h,
+                                                     (__nv_bfloat16*)out, lse);
   FITB200_CHECK_LAUNCH("attn_mma");
   return FITB200_OK;
 }

@@ -132,58 +132,74 @@ __global__ void cond_combine_kernel(const float* __restrict__ t_emb, int t_rows,
 }
 
 // --------------------------------------------------------------------------------------------
-// LayerNorm + modulate: one warp per row, row cached in registers (D <= 2048, D % 8 == 0)
+// LayerNorm + modulate.  One CTA = LN_ROWS consecutive rows of ONE sample: (1 + scale) and shift of that sample are
+// staged once in shared memory (they are 4x the bytes of a bf16 row, so re-reading them per row from L2 made the first
+// version L2-bound at 29 % of HBM peak); one warp per row, row cached in registers (D <= 2048, D % 8 == 0), 16-byte accesses.
 // --------------------------------------------------------------------------------------------
-constexpr int LN_MAXV = 8;  // 8 vectors of 8 per lane
+constexpr int LN_MAXV = 8;    // 8 vectors of 8 per lane
+constexpr int LN_ROWS = 32;   // rows per CTA (8 warps x 4 rows)
 
-template <typename InT, typename OutT>
+template <typename InT, typename OutT, int NV>
 __global__ void __launch_bounds__(256) ln_modulate_kernel(const InT* __restrict__ x, int M, int D, int rows_per_sample,
-                                                          const float* __restrict__ shift, const float* __restrict__ scale,
-                                                          long ld_mod, OutT* __restrict__ out, float* __restrict__ mean_out,
-                                                          float* __restrict__ rstd_out) {
-  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (row >= M) return;
+                                                          int blocks_per_sample, const float* __restrict__ shift,
+                                                          const float* __restrict__ scale, long ld_mod, OutT* __restrict__ out,
+                                                          float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  extern __shared__ __align__(16) float ln_mod[];  // [D] 1+scale | [D] shift
+  const int sample = blockIdx.x / blocks_per_sample, blk = blockIdx.x - sample * blocks_per_sample;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nvec = D >> 3;
-  const InT* xr = x + (size_t)row * D;
-  Vec8<InT> v[LN_MAXV];
-  float s = 0.f;
+  const size_t mrow = (size_t)sample * ld_mod;
+  for (int i = threadIdx.x; i < D / 4; i += blockDim.x) {
+    float4 sc = *reinterpret_cast<const float4*>(scale + mrow + i * 4);
+    const float4 sh = *reinterpret_cast<const float4*>(shift + mrow + i * 4);
+    sc.x += 1.0f; sc.y += 1.0f; sc.z += 1.0f; sc.w += 1.0f;
+    *reinterpret_cast<float4*>(ln_mod + i * 4) = sc;
+    *reinterpret_cast<float4*>(ln_mod + D + i * 4) = sh;
+  }
+  __syncthreads();
+  const int r_end = min(rows_per_sample, (blk + 1) * LN_ROWS);
+  for (int rl = blk * LN_ROWS + warp; rl < r_end; rl += 8) {
+    const int row = sample * rows_per_sample + rl;
+    if (row >= M) break;
+    const InT* xr = x + (size_t)row * D;
+    Vec8<InT> v[NV];
+    float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < LN_MAXV; ++i) {
-    int vi = lane + i * 32;
-    if (vi < nvec) {
-      v[i] = Vec8<InT>::load(xr + vi * 8);
+    for (int i = 0; i < NV; ++i) {
+      int vi = lane + i * 32;
+      if (vi < nvec) {
+        v[i] = Vec8<InT>::load(xr + vi * 8);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) s += v[i].v[e];
+        for (int e = 0; e < 8; ++e) s += v[i].v[e];
+      }
     }
-  }
-  const float mu = warp_sum(s) / (float)D;
-  float q = 0.f;
+    const float mu = warp_sum(s) / (float)D;
+    float q = 0.f;
 #pragma unroll
-  for (int i = 0; i < LN_MAXV; ++i) {
-    int vi = lane + i * 32;
-    if (vi < nvec) {
+    for (int i = 0; i < NV; ++i) {
+      int vi = lane + i * 32;
+      if (vi < nvec) {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) { float d = v[i].v[e] - mu; q = fmaf(d, d, q); }
+        for (int e = 0; e < 8; ++e) { float d = v[i].v[e] - mu; q = fmaf(d, d, q); }
+      }
     }
-  }
-  const float rstd = rsqrtf(warp_sum(q) / (float)D + 1e-6f);
-  if (lane == 0) {
-    if (mean_out) mean_out[row] = mu;
-    if (rstd_out) rstd_out[row] = rstd;
-  }
-  const size_t mrow = (size_t)(row / rows_per_sample) * ld_mod;
-  OutT* orow = out + (size_t)row * D;
+    const float rstd = rsqrtf(warp_sum(q) / (float)D + 1e-6f);
+    if (lane == 0) {
+      if (mean_out) mean_out[row] = mu;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
+    OutT* orow = out + (size_t)row * D;
 #pragma unroll
-  for (int i = 0; i < LN_MAXV; ++i) {
-    int vi = lane + i * 32;
-    if (vi < nvec) {
-      Vec8<float> sh = Vec8<float>::load(shift + mrow + vi * 8);
-      Vec8<float> sc = Vec8<float>::load(scale + mrow + vi * 8);
-      Vec8<OutT> o;
+    for (int i = 0; i < NV; ++i) {
+      int vi = lane + i * 32;
+      if (vi < nvec) {
+        Vec8<float> sc = Vec8<float>::load(ln_mod + vi * 8);
+        Vec8<float> sh = Vec8<float>::load(ln_mod + D + vi * 8);
+        Vec8<OutT> o;
 #pragma unroll
-      for (int e = 0; e < 8; ++e) o.v[e] = fmaf((v[i].v[e] - mu) * rstd, 1.0f + sc.v[e], sh.v[e]);
-      o.store(orow + vi * 8);
+        for (int e = 0; e < 8; ++e) o.v[e] = fmaf((v[i].v[e] - mu) * rstd, sc.v[e], sh.v[e]);
+        o.store(orow + vi * 8);
+      }
     }
   }
 }
@@ -426,6 +442,25 @@ __global__ void add_i64_kernel(int64_t* __restrict__ idx, int n, int64_t delta) 
   if (i < n) idx[i] += delta;
 }
 
+template <typename InT, typename OutT>
+static void launch_ln(const void* x, int M, int D, int rows_per_sample, const float* shift, const float* scale, int64_t ld_mod,
+                      void* out, float* mean, float* rstd, cudaStream_t s) {
+  const int samples = ceil_div(M, rows_per_sample), bps = ceil_div(rows_per_sample, LN_ROWS);
+  const dim3 grid((unsigned)(samples * bps));
+  const size_t smem = (size_t)2 * D * sizeof(float);
+  const int nv = ceil_div(D >> 3, 32);
+#define FITB200_LN_CASE(NV)                                                                                              \
+  case NV:                                                                                                               \
+    ln_modulate_kernel<InT, OutT, NV><<<grid, 256, smem, s>>>((const InT*)x, M, D, rows_per_sample, bps, shift, scale, ld_mod, \
+                                                              (OutT*)out, mean, rstd);                                   \
+    break;
+  switch (nv) {
+    FITB200_LN_CASE(1) FITB200_LN_CASE(2) FITB200_LN_CASE(3) FITB200_LN_CASE(4)
+    FITB200_LN_CASE(5) FITB200_LN_CASE(6) FITB200_LN_CASE(7) FITB200_LN_CASE(8)
+  }
+#undef FITB200_LN_CASE
+}
+
 }  // namespace fitb200
 
 using namespace fitb200;
@@ -488,10 +523,10 @@ int fitb200_ln_modulate_fwd(const void* x, int x_dtype, int M, int D, int rows_p
                             fitb200_stream_t stream) {
   FITB200_CHECK_ARG(x && shift && scale && out && M > 0 && rows_per_sample > 0, "ln_modulate: bad arguments");
   FITB200_CHECK_ARG(D % 8 == 0 && D <= 32 * 8 * LN_MAXV && ld_mod % 4 == 0, "ln_modulate: D=%d must be a multiple of 8 and <= %d", D, 32 * 8 * LN_MAXV);
-  dim3 grid((unsigned)ceil_div(M, 8));
+  FITB200_CHECK_ARG(((uintptr_t)shift & 15) == 0 && ((uintptr_t)scale & 15) == 0, "ln_modulate: shift / scale must be 16-byte aligned");
   FITB200_DISPATCH_ACT(x_dtype, InT, {
     FITB200_DISPATCH_ACT(out_dtype, OutT, {
-      ln_modulate_kernel<InT, OutT><<<grid, 256, 0, (cudaStream_t)stream>>>((const InT*)x, M, D, rows_per_sample, shift, scale, ld_mod, (OutT*)out, mean, rstd);
+      launch_ln<InT, OutT>(x, M, D, rows_per_sample, shift, scale, ld_mod, out, mean, rstd, (cudaStream_t)stream);
     })
   })
   FITB200_CHECK_LAUNCH("ln_modulate");
