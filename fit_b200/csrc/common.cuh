@@ -100,7 +100,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 // accurate variant for the fp32 verification path
 __device__ __forceinline__ float silu_acc(float x) { return x / (1.0f + expf(-x)); }
 

@@ -5,7 +5,7 @@
 //   * warp 0 : TMA producer   -- cp.async.bulk.tensor 128B-swizzled A/B k-slabs into a STAGES-deep ring
 //   * warp 1 : MMA issuer     -- one thread issues tcgen05.mma (M=128, N=BN, K=16) into TMEM,
 //                                tcgen05.commit releases smem slots / publishes the accumulator
-//   * warps 2-5 : epilogue    -- per 128-byte-wide output slab: tcgen05.ld TMEM -> registers, fused
+//   * warps 2-9 : epilogue    -- (two warps per TMEM lane quarter, half a slab each) per 128-byte-wide output slab: tcgen05.ld TMEM -> registers, fused
 //                                bias / SiLU / SwiGLU / adaLN-gate + residual, 16-byte swizzled st.shared,
 //                                TMA store.  The residual slab is TMA-LOADED two slabs ahead, so the
 //                                epilogue issues no per-row global access at all (round-1 profile: the
@@ -20,8 +20,8 @@
 namespace fitb200 {
 
 constexpr int GT_BM = 128, GT_BK = 64;
-constexpr int GT_THREADS = 192;  // producer + mma + 4 epilogue warps
-constexpr int GT_EPI_THREADS = 128;
+constexpr int GT_THREADS = 320;  // producer + mma + 8 epilogue warps
+constexpr int GT_EPI_THREADS = 256;  // two warps per TMEM lane quarter: each takes half of a slab's columns
 constexpr int GT_SLAB_BYTES = GT_BM * 128;  // 128 rows x 128 bytes
 constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - 256 /*barriers*/;
 
@@ -154,6 +154,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else {
     // ------------------------------------------------------------------ epilogue warps (2..5)
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;        // which half of each slab's columns this warp handles
     const int row = quarter * 32 + lane;     // row inside the tile == TMEM lane
     const bool leader = threadIdx.x == 64;   // first epilogue thread: issues the TMA stores / residual loads
     const uint32_t sw = (uint32_t)(row & 7); // 128B-swizzle phase of this row
@@ -194,17 +195,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         ptx::named_bar_sync(1, GT_EPI_THREADS);
         const bool live = nacc < p.N;  // tile-uniform: slabs beyond N are skipped (their store would be fully clipped)
         if (live) {
-          float acc[ACCC];
+          constexpr int HACC = ACCC / 2;  // accumulator columns of this warp's half slab
+          float acc[HACC];
 #pragma unroll
-          for (int c = 0; c < ACCC / 16; ++c) tmem_ld16f(taddr + slab * ACCC + c * 16, acc + c * 16);
+          for (int c = 0; c < HACC / 16; ++c) tmem_ld16f(taddr + slab * ACCC + half * HACC + c * 16, acc + c * 16);
           ptx::tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {  // 8 x 16-byte chunks per 128-byte row
+          for (int jj = 0; jj < 4; ++jj) {  // this warp's 4 of the 8 x 16-byte chunks per 128-byte row
+            const int j = half * 4 + jj;
             float v[8];
             if (SWIGLU) {
               // packed weight: every 32 accumulator columns = 16 gate rows then the matching 16 up rows
-              const int a0 = (j >> 1) * 32 + (j & 1) * 8;
-              const int nb = nacc + a0;
+              const int a0 = (jj >> 1) * 32 + (jj & 1) * 8;  // inside this warp's half slab
+              const int nb = nacc + half * HACC + a0;
               const bool ok = nb < p.N;
               const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
               const float4 g0 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb)) : z4;
@@ -222,8 +225,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               for (int i4 = 0; i4 < CW / 4; ++i4) {
                 float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (p.bias && ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + nb + i4 * 4));
-                v[i4 * 4 + 0] = acc[j * CW + i4 * 4 + 0] + b4.x; v[i4 * 4 + 1] = acc[j * CW + i4 * 4 + 1] + b4.y;
-                v[i4 * 4 + 2] = acc[j * CW + i4 * 4 + 2] + b4.z; v[i4 * 4 + 3] = acc[j * CW + i4 * 4 + 3] + b4.w;
+                v[i4 * 4 + 0] = acc[jj * CW + i4 * 4 + 0] + b4.x; v[i4 * 4 + 1] = acc[jj * CW + i4 * 4 + 1] + b4.y;
+                v[i4 * 4 + 2] = acc[jj * CW + i4 * 4 + 2] + b4.z; v[i4 * 4 + 3] = acc[jj * CW + i4 * 4 + 3] + b4.w;
               }
               if (EPI == FITB200_EPI_BIAS_SILU) {
 #pragma unroll
