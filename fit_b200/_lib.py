@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_PKG, "libfit_b200.so")
 HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "fit_b200.h")
 
 F32, BF16 = 0, 1
-EPI_BIAS, EPI_BIAS_SILU, EPI_BIAS_GATE_RESID, EPI_SWIGLU = 0, 1, 2, 3
+EPI_BIAS, EPI_BIAS_SILU, EPI_BIAS_GATE_RESID, EPI_SWIGLU, EPI_BIAS_ROPE = 0, 1, 2, 3, 4
 
 _lib = None
 
@@ -33,6 +33,8 @@ class GemmArgs(C.Structure):
         ("epilogue", C.c_int32),
         ("gate", C.c_void_p), ("ld_gate", C.c_int64), ("rows_per_sample", C.c_int32),
         ("resid", C.c_void_p), ("ld_resid", C.c_int64), ("resid_dtype", C.c_int32),
+        ("rope_freqs", C.c_void_p), ("rope_rows", C.c_int32), ("rope_tokens", C.c_int32), ("rope_head_dim", C.c_int32),
+        ("rope_cols", C.c_int32),
     ]
 
 

@@ -8,6 +8,8 @@ namespace fitb200 {
 
 int attn_fwd_f32(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask,
                  int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s);
+int attn_fwd_tc(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask,
+                int R, int Tn, int h, int d, int prerotated, void* out, float* lse, cudaStream_t s);
 
 constexpr int AM_BQ = 128;      // queries per CTA: 8 warps x 16 rows
 constexpr int AM_BK = 64;       // keys per softmax tile
@@ -71,8 +73,10 @@ __device__ __forceinline__ void load_rotate_rows(__nv_bfloat16* dst, const __nv_
       if (live[u]) {
         const size_t t = (size_t)(t0 + row);
         raw[u] = *reinterpret_cast<const uint4*>(src + t * gstride + c * 8);
-        f0[u] = __ldg(reinterpret_cast<const float4*>(fr + t * HD + c * 8));
-        f1[u] = __ldg(reinterpret_cast<const float4*>(fr + t * HD + c * 8 + 4));
+        if (fr) {  // fr == nullptr: q / k were rotated by the qkv GEMM epilogue
+          f0[u] = __ldg(reinterpret_cast<const float4*>(fr + t * HD + c * 8));
+          f1[u] = __ldg(reinterpret_cast<const float4*>(fr + t * HD + c * 8 + 4));
+        }
       }
     }
 #pragma unroll
@@ -80,7 +84,7 @@ __device__ __forceinline__ void load_rotate_rows(__nv_bfloat16* dst, const __nv_
       const int i = i0 + u * AM_THREADS;
       if (i < total) {
         const int row = i / CHP, c = i - row * CHP;
-        *reinterpret_cast<uint4*>(dst + row * LDS + c * 8) = live[u] ? rotate8(raw[u], f0[u], f1[u]) : make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(dst + row * LDS + c * 8) = live[u] ? (fr ? rotate8(raw[u], f0[u], f1[u]) : raw[u]) : make_uint4(0, 0, 0, 0);
       }
     }
   }
@@ -112,7 +116,7 @@ __global__ void __launch_bounds__(AM_THREADS, 2) attn_mma_kernel(const __nv_bflo
   const int kvl = min(kv_len[r], Tn);
   const size_t row_stride = (size_t)3 * h * HD;
   const __nv_bfloat16* base = qkv + (size_t)r * Tn * row_stride + (size_t)head * HD;
-  const float* fr = freqs + (size_t)(freqs_rows == 1 ? 0 : r) * Tn * HD;
+  const float* fr = freqs ? freqs + (size_t)(freqs_rows == 1 ? 0 : r) * Tn * HD : nullptr;
   const int D = h * HD;
 
   if (q0 >= kvl) {  // padded query tile: zero output rows, no work
@@ -287,14 +291,19 @@ static int launch_attn_mma(const void* qkv, const float* freqs, int freqs_rows, 
 using namespace fitb200;
 
 extern "C" int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, int freqs_rows, const int32_t* kv_len,
-                                const uint8_t* mask, int R, int T, int h, int d, void* out, float* lse,
+                                const uint8_t* mask, int R, int T, int h, int d, int flags, void* out, float* lse,
                                 fitb200_stream_t stream) {
-  FITB200_CHECK_ARG(qkv && freqs && kv_len && out && R > 0 && T > 0 && h > 0, "attn_fwd: bad arguments");
-  FITB200_CHECK_ARG(freqs_rows == 1 || freqs_rows == R, "attn_fwd: freqs_rows must be 1 or R");
+  const int pre = flags & FITB200_ATTN_PREROTATED;
+  FITB200_CHECK_ARG(qkv && (freqs || pre) && kv_len && out && R > 0 && T > 0 && h > 0, "attn_fwd: bad arguments");
+  FITB200_CHECK_ARG(pre || freqs_rows == 1 || freqs_rows == R, "attn_fwd: freqs_rows must be 1 or R");
   FITB200_CHECK_ARG(h <= 65535 && R <= 65535, "attn_fwd: h and R must be <= 65535");
   cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == FITB200_F32 && pre) { set_last_error("attn_fwd: PREROTATED is a bf16-path flag"); return FITB200_ERR_UNSUPPORTED; }
   if (dtype == FITB200_F32) return attn_fwd_f32(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, d, out, lse, s);
   if (dtype == FITB200_BF16) {
+    // sequences that fit the resident K/V tile (every trained shape): tcgen05 kernel; longer (extrapolation): chunked mma.sync kernel
+    if (T <= 256 && (d == 64 || d == 72)) return attn_fwd_tc(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, d, pre, out, lse, s);
+    if (pre) freqs = nullptr;
     if (d == 64) return launch_attn_mma<64>(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, out, lse, s);
     if (d == 72) return launch_attn_mma<72>(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, out, lse, s);
     set_last_error("attn_fwd: head_dim %d not supported (64 or 72)", d);

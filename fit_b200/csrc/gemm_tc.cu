@@ -41,6 +41,7 @@ struct GtParams {
   int M, N, K;
   const float* bias;
   const float* gate; long ld_gate; int rows_per_sample;
+  const float* rope_freqs; int rope_rows, rope_tokens, rope_hd, rope_cols;
 };
 
 __device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
@@ -59,6 +60,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int STAGES = Cfg::STAGES;
   constexpr bool SWIGLU = EPI == FITB200_EPI_SWIGLU;
   constexpr bool RESID = EPI == FITB200_EPI_BIAS_GATE_RESID;
+  constexpr bool ROPE = EPI == FITB200_EPI_BIAS_ROPE;
   constexpr int OUTC = 128 / (int)sizeof(OutT);       // output columns per slab
   constexpr int ACCC = SWIGLU ? 2 * OUTC : OUTC;      // accumulator columns per slab
   constexpr int NSLAB = BN / ACCC;
@@ -179,6 +181,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int m = min(m0 + row, p.M - 1);
       const float* gate_row = nullptr;
       if (RESID) gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
+      const float* rope_row = nullptr;  // (cos, sin) pairs of this row's token
+      if (ROPE) {
+        const int smp = m / p.rope_tokens, tok = m - smp * p.rope_tokens;
+        rope_row = p.rope_freqs + ((size_t)(p.rope_rows == 1 ? 0 : smp) * p.rope_tokens + tok) * p.rope_hd;
+      }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
@@ -197,6 +204,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (live) {
           constexpr int HACC = ACCC / 2;  // accumulator columns of this warp's half slab
           float acc[HACC];
+          // RoPE table of this thread's 4 chunks, issued ahead of the TMEM loads (L2 latency hidden behind them)
+          float4 fq[ROPE ? 4 : 1][CW / 4];
+          if (ROPE) {
+            int hcol = (nacc + half * 4 * CW) % p.rope_hd;  // head-dim index of the first chunk (chunks never straddle a head: 8 | head_dim)
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+              const bool rot = nacc + (half * 4 + jj) * CW < p.rope_cols;
+#pragma unroll
+              for (int i4 = 0; i4 < CW / 4; ++i4)
+                fq[ROPE ? jj : 0][i4] = rot ? __ldg(reinterpret_cast<const float4*>(rope_row + hcol + i4 * 4)) : make_float4(1.f, 0.f, 1.f, 0.f);
+              hcol += CW;
+              if (hcol >= p.rope_hd) hcol -= p.rope_hd;
+            }
+          }
 #pragma unroll
           for (int c = 0; c < HACC / 16; ++c) tmem_ld16f(taddr + slab * ACCC + half * HACC + c * 16, acc + c * 16);
           ptx::tmem_ld_wait();
@@ -227,6 +248,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (p.bias && ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + nb + i4 * 4));
                 v[i4 * 4 + 0] = acc[jj * CW + i4 * 4 + 0] + b4.x; v[i4 * 4 + 1] = acc[jj * CW + i4 * 4 + 1] + b4.y;
                 v[i4 * 4 + 2] = acc[jj * CW + i4 * 4 + 2] + b4.z; v[i4 * 4 + 3] = acc[jj * CW + i4 * 4 + 3] + b4.w;
+              }
+              if (ROPE) {  // complex_mult (fit.py:152-154): (a + ib)(c + id), pairs (2j, 2j+1); identity (1, 0) on the v columns
+#pragma unroll
+                for (int i4 = 0; i4 < CW / 4; ++i4) {
+                  const float4 f = fq[ROPE ? jj : 0][i4];
+                  const float a0 = v[i4 * 4 + 0], b0 = v[i4 * 4 + 1], a1 = v[i4 * 4 + 2], b1 = v[i4 * 4 + 3];
+                  v[i4 * 4 + 0] = a0 * f.x - b0 * f.y; v[i4 * 4 + 1] = b0 * f.x + a0 * f.y;
+                  v[i4 * 4 + 2] = a1 * f.z - b1 * f.w; v[i4 * 4 + 3] = b1 * f.z + a1 * f.w;
+                }
               }
               if (EPI == FITB200_EPI_BIAS_SILU) {
 #pragma unroll
@@ -338,6 +368,7 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   GtParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.bias = a.bias;
   p.gate = a.gate; p.ld_gate = a.ld_gate; p.rows_per_sample = a.rows_per_sample;
+  p.rope_freqs = a.rope_freqs; p.rope_rows = a.rope_rows; p.rope_tokens = a.rope_tokens; p.rope_hd = a.rope_head_dim; p.rope_cols = a.rope_cols;
   auto kern = gemm_tc_kernel<BN, EPI, OutT>;
   static bool attr_done = false;  // per template instantiation
   if (!attr_done) {
@@ -357,6 +388,7 @@ static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
   switch (a.epilogue) {
     case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT>(a, s);
     case FITB200_EPI_BIAS_SILU: return launch_tc<BN, FITB200_EPI_BIAS_SILU, OutT>(a, s);
+    case FITB200_EPI_BIAS_ROPE: return launch_tc<BN, FITB200_EPI_BIAS_ROPE, OutT>(a, s);
     case FITB200_EPI_SWIGLU:
       if constexpr (BN != 192) return launch_tc<BN, FITB200_EPI_SWIGLU, OutT>(a, s);  // 128 accumulator columns per slab
       break;
@@ -394,6 +426,10 @@ extern "C" int fitb200_gemm_bf16_tc(const fitb200_gemm_args* ap, fitb200_stream_
   FITB200_CHECK_ARG(a.N % 8 == 0 && a.ldo % 8 == 0, "gemm_bf16_tc: N and ldo must be multiples of 8 (N=%d)", a.N);
   FITB200_CHECK_ARG(a.bias == nullptr || ((uintptr_t)a.bias & 15) == 0, "gemm_bf16_tc: bias must be 16-byte aligned");
   if (a.epilogue == FITB200_EPI_SWIGLU) FITB200_CHECK_ARG(a.N % 32 == 0 && a.bias, "gemm_bf16_tc: SWIGLU needs N %% 32 == 0 and a packed bias");
+  if (a.epilogue == FITB200_EPI_BIAS_ROPE)
+    FITB200_CHECK_ARG(a.rope_freqs && ((uintptr_t)a.rope_freqs & 15) == 0 && a.rope_tokens > 0 && a.rope_head_dim > 0 && a.rope_head_dim % 8 == 0 &&
+                          a.rope_cols % a.rope_head_dim == 0 && a.rope_cols <= a.N && (a.rope_rows == 1 || (int64_t)a.rope_rows * a.rope_tokens >= a.M),
+                      "gemm_bf16_tc: BIAS_ROPE needs a 16-byte aligned fp32 table [1|samples, tokens, head_dim], head_dim %% 8 == 0, rope_cols a multiple of head_dim");
   if (a.epilogue == FITB200_EPI_BIAS_GATE_RESID)
     FITB200_CHECK_ARG(a.gate && a.resid && a.rows_per_sample > 0 && a.ld_gate % 4 == 0 && a.ld_resid % 8 == 0 &&
                           ((uintptr_t)a.gate & 15) == 0 && ((uintptr_t)a.resid & 15) == 0 && a.resid_dtype == a.out_dtype,

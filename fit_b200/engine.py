@@ -19,7 +19,7 @@ from typing import Dict, Optional, Tuple
 import torch
 
 from . import ops
-from ._lib import EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_SILU, EPI_SWIGLU
+from ._lib import EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_ROPE, EPI_BIAS_SILU, EPI_SWIGLU
 
 Tensor = torch.Tensor
 
@@ -173,8 +173,14 @@ class FiTEngine:
         sh1, sc1, g1, sh2, sc2, g2 = ws.mod_views[i]
         nm = W.n_mod
         ops.ln_modulate(ws.xs, sh1, sc1, nm, T, ws.h)
-        ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS)
-        ops.attention(ws.qkv, pos, ws.kv_len, mask, R, T, m.num_heads, D // m.num_heads, ws.att)
+        if self.precision == "bf16":
+            # apply_rotary_emb (fit.py:160-174) rides in the qkv GEMM epilogue (fp32 accumulators, q and k columns), so the
+            # attention kernel fetches finished operands with TMA
+            ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS_ROPE, rope=pos, rope_cols=2 * D)
+            ops.attention(ws.qkv, None, ws.kv_len, mask, R, T, m.num_heads, D // m.num_heads, ws.att, prerotated=True)
+        else:
+            ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS)
+            ops.attention(ws.qkv, pos, ws.kv_len, mask, R, T, m.num_heads, D // m.num_heads, ws.att)
         ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=nm, rows_per_sample=T, resid=ws.xs)
         ops.ln_modulate(ws.xs, sh2, sc2, nm, T, ws.h)
         if self.precision == "bf16":
@@ -208,6 +214,7 @@ class FiTEngine:
             raise ValueError(f"pos shape {tuple(pos.shape)} does not match (1|{R}, {T}, {D // m.num_heads})")
         if pos.dtype != torch.float32:
             raise TypeError("fit_b200: pos must be fp32 (cos, sin) pairs")
+        pos = pos.contiguous()
         W = self.weights()
         ws = self.workspace(R, T, x.device)
         t = t.to(torch.int64) if t.dtype != torch.int64 else t

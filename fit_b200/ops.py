@@ -11,7 +11,7 @@ from typing import Optional
 import torch
 
 from . import _lib as L
-from ._lib import BF16, EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_SILU, EPI_SWIGLU, F32  # noqa: F401
+from ._lib import BF16, EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_ROPE, EPI_BIAS_SILU, EPI_SWIGLU, F32  # noqa: F401
 
 Tensor = torch.Tensor
 
@@ -64,7 +64,8 @@ def cond_combine(t_emb: Tensor, y: Tensor, table: Tensor, c: Optional[Tensor], s
 
 def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: int = EPI_BIAS, *, M: Optional[int] = None,
          B2: Optional[Tensor] = None, bias2: Optional[Tensor] = None, gate: Optional[Tensor] = None, ld_gate: int = 0,
-         rows_per_sample: int = 1, resid: Optional[Tensor] = None, N: Optional[int] = None):
+         rows_per_sample: int = 1, resid: Optional[Tensor] = None, N: Optional[int] = None,
+         rope: Optional[Tensor] = None, rope_cols: int = 0):
     """out = epilogue(A @ B^T).  A [M,K] and B [N,K] both fp32 (CUDA-core path) or both bf16 (tcgen05 path).
     ``gate`` may be a strided view: pass the storage-offset view and its row stride ``ld_gate``."""
     L.require_cuda(A, B, out)
@@ -84,6 +85,9 @@ def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: in
     a.resid = 0 if resid is None else resid.data_ptr()
     a.ld_resid = 0 if resid is None else resid.stride(0)
     a.resid_dtype = F32 if resid is None else L.dtype_code(resid)
+    if rope is not None:   # EPI_BIAS_ROPE: fp32 table [1|samples, tokens, head_dim]
+        assert rope.dtype == torch.float32 and rope.dim() == 3 and rope.is_contiguous()
+        a.rope_freqs, a.rope_rows, a.rope_tokens, a.rope_head_dim, a.rope_cols = rope.data_ptr(), rope.shape[0], rope.shape[1], rope.shape[2], rope_cols
     if A.dtype == torch.float32 and B.dtype == torch.float32:
         fn, what = L.lib().fitb200_gemm_f32, "gemm_f32"
     elif A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16:
@@ -105,16 +109,24 @@ def ln_modulate(x: Tensor, shift: Tensor, scale: Tensor, ld_mod: int, rows_per_s
     return out
 
 
-def attention(qkv: Tensor, freqs: Tensor, kv_len: Tensor, mask: Optional[Tensor], R: int, T: int, h: int, d: int,
-              out: Tensor, lse: Optional[Tensor] = None):
-    """qkv [R*T, 3*h*d] -> out [R*T, h*d]; RoPE + key-masked softmax attention."""
-    L.require_cuda(qkv, freqs, kv_len, out)
-    assert freqs.dtype == torch.float32 and kv_len.dtype == torch.int32
+def attention(qkv: Tensor, freqs: Optional[Tensor], kv_len: Tensor, mask: Optional[Tensor], R: int, T: int, h: int, d: int,
+              out: Tensor, lse: Optional[Tensor] = None, prerotated: bool = False):
+    """qkv [R*T, 3*h*d] -> out [R*T, h*d]; RoPE + key-masked softmax attention.
+    prerotated: q / k already rotated by a gemm(..., EPI_BIAS_ROPE) (bf16 path)."""
+    L.require_cuda(qkv, kv_len, out)
+    assert kv_len.dtype == torch.int32
+    if prerotated:
+        L.check(L.lib().fitb200_attn_fwd(L.ptr(_c(qkv)), L.dtype_code(qkv), None, 1, L.ptr(kv_len),
+                                         L.ptr(None if mask is None else _c(mask.view(torch.uint8) if mask.dtype == torch.bool else mask)),
+                                         R, T, h, d, 1, L.ptr(out), L.ptr(lse), L.stream_ptr()), "attn_fwd")
+        return out
+    L.require_cuda(freqs)
+    assert freqs.dtype == torch.float32
     m8 = None
     if mask is not None:
         m8 = _c(mask.view(torch.uint8) if mask.dtype == torch.bool else mask)
     fr = 1 if freqs.dim() == 2 else freqs.shape[0]
-    L.check(L.lib().fitb200_attn_fwd(L.ptr(_c(qkv)), L.dtype_code(qkv), L.ptr(_c(freqs)), fr, L.ptr(kv_len), L.ptr(m8), R, T, h, d,
+    L.check(L.lib().fitb200_attn_fwd(L.ptr(_c(qkv)), L.dtype_code(qkv), L.ptr(_c(freqs)), fr, L.ptr(kv_len), L.ptr(m8), R, T, h, d, 0,
                                      L.ptr(out), L.ptr(lse), L.stream_ptr()), "attn_fwd")
     return out
 

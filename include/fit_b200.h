@@ -32,7 +32,9 @@ enum {
   FITB200_EPI_BIAS = 0,            /* out = acc + bias                      qkv (fit.py:234), adaLN (fit.py:323-324,329) */
   FITB200_EPI_BIAS_SILU = 1,       /* out = silu(acc + bias)                t-embedder first Linear (fit.py:55-57) */
   FITB200_EPI_BIAS_GATE_RESID = 2, /* out = resid + gate[sample] * (acc+bias)   proj / fc2 + adaLN-Zero gate + residual (fit.py:331-337) */
-  FITB200_EPI_SWIGLU = 3           /* out = silu(acc_g + b_g) * (acc_x + b_x)   SwiGLU fc1_g|fc1_x (fit.py:278-280) */
+  FITB200_EPI_SWIGLU = 3,          /* out = silu(acc_g + b_g) * (acc_x + b_x)   SwiGLU fc1_g|fc1_x (fit.py:278-280) */
+  FITB200_EPI_BIAS_ROPE = 4        /* out = rope(acc + bias): qkv Linear (fit.py:234) fused with apply_rotary_emb (fit.py:160-174) on the
+                                      q and k columns [0, rope_cols); bf16 tcgen05 GEMM only */
 };
 
 const char* fitb200_last_error(void);
@@ -83,6 +85,10 @@ typedef struct {
   int32_t epilogue;                /* FITB200_EPI_* */
   const float* gate; int64_t ld_gate; int32_t rows_per_sample; /* GATE_RESID: gate[(m / rows_per_sample) * ld_gate + n] */
   const void* resid; int64_t ld_resid; int32_t resid_dtype;    /* GATE_RESID: may alias out */
+  /* BIAS_ROPE: output row m is token m % rope_tokens of sample m / rope_tokens; column n < rope_cols belongs to head-dim index
+   * n % rope_head_dim; the pair (2j, 2j+1) is rotated by (cos, sin) = rope_freqs[(s or 0), token, 2j .. 2j+1]
+   * (fp32 [rope_rows = 1 | samples, rope_tokens, rope_head_dim], the table of pos_embed.py:51-75). */
+  const float* rope_freqs; int32_t rope_rows, rope_tokens, rope_head_dim, rope_cols;
 } fitb200_gemm_args;
 
 /* fp32 FMA GEMM on CUDA cores: A, B, B2 fp32.  The fp32 verification mode and the small
@@ -111,9 +117,13 @@ int fitb200_ln_modulate_fwd(const void* x, int x_dtype, int M, int D, int rows_p
  * Query tiles starting at or beyond kv_len[r] are skipped and their output rows zero-filled (they are
  * padding whose reference output is unspecified).  out: [R, T, h*d].
  * lse: optional fp32 [R, h, T] log-sum-exp (natural log, of the scaled scores) for backward.
- * d in {64, 72}. */
+ * d in {64, 72}.
+ * flags: FITB200_ATTN_PREROTATED = q and k in qkv already carry the RoPE (written by a FITB200_EPI_BIAS_ROPE GEMM);
+ *        freqs is then ignored (may be NULL).  bf16 only.
+ * bf16, T <= 256: tcgen05 / TMEM kernel (attn_tc.cu); bf16, T > 256: chunked mma.sync kernel; fp32: CUDA-core kernel. */
+enum { FITB200_ATTN_PREROTATED = 1 };
 int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, int freqs_rows, const int32_t* kv_len,
-                     const uint8_t* mask, int R, int T, int h, int d, void* out, float* lse,
+                     const uint8_t* mask, int R, int T, int h, int d, int flags, void* out, float* lse,
                      fitb200_stream_t stream);
 
 /* ---- final layer ---------------------------------------------------------------------------------

@@ -124,3 +124,30 @@ def test_gemm_argument_errors(ops):
         ops.gemm(A.float(), B, None, out, EPI_BIAS)
     with pytest.raises(RuntimeError, match="CUDA tensors"):
         ops.gemm(A.cpu(), B.cpu(), None, out.cpu(), EPI_BIAS)
+
+
+@pytest.mark.parametrize("odt", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("R,T,h,d,rows", [(2, 256, 16, 72, 1), (3, 200, 12, 64, 3), (2, 64, 2, 72, 2), (4, 33, 2, 64, 1)])
+def test_gemm_qkv_rope_epilogue(ops, odt, R, T, h, d, rows):
+    """EPI_BIAS_ROPE: qkv Linear (fit.py:234) + apply_rotary_emb on the q and k columns (fit.py:160-174), v untouched."""
+    from oracle import fit_oracle as fo
+    from oracle.pos_embed_oracle import precompute_freqs_cis_2d
+    import numpy as np
+    D, M = h * d, R * T
+    A, B, bias = _inputs(M, 3 * D, D, R * T + d, torch.bfloat16)
+    g = torch.Generator().manual_seed(3)
+    side = int(np.ceil(np.sqrt(T)))
+    tab = torch.tensor(precompute_freqs_cis_2d(d, side, side, max_length=256), dtype=torch.float32)[:T]
+    freqs = tab[None].repeat(rows, 1, 1).contiguous()
+    if rows > 1:   # per-sample tables (mixed resolution / masked_FiT permuted tokens): make them differ
+        for r in range(rows):
+            freqs[r] = tab[torch.randperm(T, generator=g)]
+    lin = (A.double() @ B.double().t() + bias.double()).view(R, T, 3, h, d)
+    q, k, v = lin.permute(2, 0, 3, 1, 4)
+    fr = freqs.double()
+    want = torch.stack([fo.rope_rotate(q, fr), fo.rope_rotate(k, fr), v], 0).permute(1, 3, 0, 2, 4).reshape(M, 3 * D)
+    out = torch.empty(M, 3 * D, dtype=odt, device="cuda")
+    ops.gemm(A.cuda(), B.cuda(), bias.cuda(), out, 4, rope=freqs.cuda(), rope_cols=2 * D)
+    tol = 1e-5 if odt == torch.float32 else 4e-3
+    assert rel_l2(out.float(), want) < tol
+    assert rel_l2(out.float()[:, 2 * D:], want[:, 2 * D:]) < tol

@@ -234,6 +234,9 @@ def _attn_oracle(qkv, freqs, mask):
     (64, 2, 64, [64, 50, 64, 36], True),
     (400, 4, 72, [400, 400], False),
     (96, 3, 72, [96, 10, 33], True),
+    (256, 2, 72, [16, 17, 128, 129, 144, 255], False),
+    (200, 2, 64, [200, 128, 7, 160], True),
+    (8, 1, 64, [8, 3], False),
 ])
 def test_attention(ops, dt, T, h, d, lens, nonprefix):
     R = len(lens)
@@ -249,6 +252,25 @@ def test_attention(ops, dt, T, h, d, lens, nonprefix):
     tol = 2e-5 if dt == torch.float32 else 8e-3
     for r, L in enumerate(lens):   # compare the valid tokens only
         assert rel_l2(out[r, :L], want[r, :L]) < tol, (r, L)
+    # log-sum-exp of the scaled, key-masked scores (saved for the backward pass)
+    q, k, _ = qkv.permute(2, 0, 3, 1, 4)
+    q, k = fo.rope_rotate(q, freqs), fo.rope_rotate(k, freqs)
+    sc = (q @ k.transpose(-1, -2)) * d ** -0.5
+    sc = sc.masked_fill(~mask[:, None, None, :], float("-inf"))
+    want_lse = torch.logsumexp(sc, -1)
+    for r, L in enumerate(lens):
+        assert (lse[r, :, :L].cpu() - want_lse[r, :, :L]).abs().max() < (1e-4 if dt == torch.float32 else 3e-2), (r, L)
+    if dt == torch.bfloat16:
+        # pre-rotated operands (the qkv GEMM's EPI_BIAS_ROPE epilogue wrote rope(q), rope(k)): TMA-fed tcgen05 kernel for T <= 256
+        q3, k3, v3 = qkv.permute(2, 0, 3, 1, 4)
+        qr, kr = fo.rope_rotate(q3, freqs).bfloat16().float(), fo.rope_rotate(k3, freqs).bfloat16().float()
+        want2 = fo.attention_core(qr, kr, v3, mask).transpose(1, 2).reshape(R, T, -1)
+        qkv_rot = torch.stack([qr, kr, v3], 0).permute(1, 3, 0, 2, 4).contiguous().bfloat16()   # [R, T, 3, h, d]
+        out2 = torch.empty(R * T, h * d, dtype=dt, device="cuda")
+        ops.attention(qkv_rot.cuda().view(R * T, 3 * h * d), None, kv, mask.cuda(), R, T, h, d, out2, prerotated=True)
+        out2 = out2.float().cpu().view(R, T, h * d)
+        for r, L in enumerate(lens):
+            assert rel_l2(out2[r, :L], want2[r, :L]) < 5e-3, ("prerotated", r, L)
     # broadcast table (freqs_rows = 1) on full-length rows
     if all(L == T for L in lens) and not nonprefix:
         out1 = torch.empty(R * T, h * d, dtype=dt, device="cuda")

@@ -37,7 +37,8 @@ def test_gemm_args_struct_matches_header_layout():
     assert GemmArgs.lda.offset == 24 and GemmArgs.B2.offset == 48 and GemmArgs.out.offset == 72
     assert GemmArgs.out_dtype.offset == 88 and GemmArgs.epilogue.offset == 92 and GemmArgs.gate.offset == 96
     assert GemmArgs.rows_per_sample.offset == 112 and GemmArgs.resid.offset == 120 and GemmArgs.resid_dtype.offset == 136
-    assert ctypes.sizeof(GemmArgs) == 144
+    assert GemmArgs.rope_freqs.offset == 144 and GemmArgs.rope_rows.offset == 152 and GemmArgs.rope_cols.offset == 164
+    assert ctypes.sizeof(GemmArgs) == 168
 
 
 @pytest.mark.parametrize("rs", ["10", "250", "ddim25", ""])
