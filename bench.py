@@ -170,7 +170,7 @@ def kernel_rooflines(model, sampler, peaks, iters=5):
     """Per-kernel roofline, timed alone with CUDA events on the launch stream (L2 flushed between iterations)."""
     import torch
     from fit_b200 import ops
-    from fit_b200._lib import EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_SWIGLU
+    from fit_b200._lib import EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_ROPE, EPI_SWIGLU
     eng = model.engine
     W = eng.weights()
     ws = eng.workspace(2 * sampler.B, sampler.T, sampler.device)
@@ -195,12 +195,13 @@ def kernel_rooflines(model, sampler, peaks, iters=5):
 
     add("gemm_tc[swiglu fc1_g|fc1_x]", lambda: ops.gemm(ws.h, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU),
         2.0 * M * D * 2 * Hp, (M * D + 2 * Hp * D + M * Hp) * 2)
-    add("gemm_tc[qkv]", lambda: ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS), 2.0 * M * D * 3 * D, (M * D + 3 * D * D + M * 3 * D) * 2)
+    add("gemm_tc[qkv+rope]", lambda: ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS_ROPE, rope=sampler.pos, rope_cols=2 * D),
+        2.0 * M * D * 3 * D, (M * D + 3 * D * D + M * 3 * D) * 2)
     add("gemm_tc[fc2+gate+resid]", lambda: ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=W.n_mod,
                                                      rows_per_sample=T, resid=ws.xs), 2.0 * M * Hp * D, (M * Hp + D * Hp) * 2 + 2 * M * D * bpe)
     add("gemm_tc[proj+gate+resid]", lambda: ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=W.n_mod,
                                                       rows_per_sample=T, resid=ws.xs), 2.0 * M * D * D, (M * D + D * D) * 2 + 2 * M * D * bpe)
-    add("attn_fwd[rope+softmax]", lambda: ops.attention(ws.qkv, sampler.pos, ws.kv_len, sampler.mask, 2 * sampler.B, T, h, dh, ws.att),
+    add("attn_tc[softmax(qk^T)v]", lambda: ops.attention(ws.qkv, None, ws.kv_len, sampler.mask, 2 * sampler.B, T, h, dh, ws.att, prerotated=True),
         4.0 * (2 * sampler.B) * T * T * D, (M * 3 * D + M * D) * 2)
     add("ln_modulate", lambda: ops.ln_modulate(ws.xs, sh1, sc1, W.n_mod, T, ws.h), 0.0, M * D * (bpe + 2))
     tb = sampler.diffusion._tables(sampler.device)
