@@ -35,6 +35,7 @@ class GemmArgs(C.Structure):
         ("resid", C.c_void_p), ("ld_resid", C.c_int64), ("resid_dtype", C.c_int32),
         ("rope_freqs", C.c_void_p), ("rope_rows", C.c_int32), ("rope_tokens", C.c_int32), ("rope_head_dim", C.c_int32),
         ("rope_cols", C.c_int32),
+        ("a_mn", C.c_int32), ("b_mn", C.c_int32),
     ]
 
 

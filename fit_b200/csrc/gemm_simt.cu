@@ -27,13 +27,31 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(fitb200_gemm_args a) {
   for (int k0 = 0; k0 < K; k0 += SG_BK) {
     float4 av = make_float4(0.f, 0.f, 0.f, 0.f), bv = av, b2v = av;
     const int kk = k0 + lk;
-    if (m0 + lrow < M && kk < K) av = *reinterpret_cast<const float4*>(A + (size_t)(m0 + lrow) * a.lda + kk);
-    if (n0 + lrow < N && kk < K) {
-      bv = *reinterpret_cast<const float4*>(B + (size_t)(n0 + lrow) * a.ldb + kk);
-      if (EPI == FITB200_EPI_SWIGLU) b2v = *reinterpret_cast<const float4*>(B2 + (size_t)(n0 + lrow) * a.ldb + kk);
+    // contraction-major operands (backward GEMMs): thread -> k-row tid >> 4, 4 consecutive m / n at (tid & 15) * 4
+    const int tk = k0 + (tid >> 4), tmn = (tid & 15) * 4;
+    if (a.a_mn) {
+      float t[4] = {0.f, 0.f, 0.f, 0.f};
+      if (tk < K)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (m0 + tmn + i < M) t[i] = A[(size_t)tk * a.lda + m0 + tmn + i];
+      As[tid >> 4][tmn + 0] = t[0]; As[tid >> 4][tmn + 1] = t[1]; As[tid >> 4][tmn + 2] = t[2]; As[tid >> 4][tmn + 3] = t[3];
+    } else {
+      if (m0 + lrow < M && kk < K) av = *reinterpret_cast<const float4*>(A + (size_t)(m0 + lrow) * a.lda + kk);
+      As[lk + 0][lrow] = av.x; As[lk + 1][lrow] = av.y; As[lk + 2][lrow] = av.z; As[lk + 3][lrow] = av.w;
     }
-    As[lk + 0][lrow] = av.x; As[lk + 1][lrow] = av.y; As[lk + 2][lrow] = av.z; As[lk + 3][lrow] = av.w;
-    Bs[lk + 0][lrow] = bv.x; Bs[lk + 1][lrow] = bv.y; Bs[lk + 2][lrow] = bv.z; Bs[lk + 3][lrow] = bv.w;
+    if (a.b_mn) {
+      float t[4] = {0.f, 0.f, 0.f, 0.f};
+      if (tk < K)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (n0 + tmn + i < N) t[i] = B[(size_t)tk * a.ldb + n0 + tmn + i];
+      Bs[tid >> 4][tmn + 0] = t[0]; Bs[tid >> 4][tmn + 1] = t[1]; Bs[tid >> 4][tmn + 2] = t[2]; Bs[tid >> 4][tmn + 3] = t[3];
+    } else {
+      if (n0 + lrow < N && kk < K) {
+        bv = *reinterpret_cast<const float4*>(B + (size_t)(n0 + lrow) * a.ldb + kk);
+        if (EPI == FITB200_EPI_SWIGLU) b2v = *reinterpret_cast<const float4*>(B2 + (size_t)(n0 + lrow) * a.ldb + kk);
+      }
+      Bs[lk + 0][lrow] = bv.x; Bs[lk + 1][lrow] = bv.y; Bs[lk + 2][lrow] = bv.z; Bs[lk + 3][lrow] = bv.w;
+    }
     if (EPI == FITB200_EPI_SWIGLU) {
       Bs2[lk + 0][lrow] = b2v.x; Bs2[lk + 1][lrow] = b2v.y; Bs2[lk + 2][lrow] = b2v.z; Bs2[lk + 3][lrow] = b2v.w;
     }
@@ -115,7 +133,9 @@ extern "C" int fitb200_gemm_f32(const fitb200_gemm_args* ap, fitb200_stream_t st
   FITB200_CHECK_ARG(ap, "gemm_f32: null args");
   const fitb200_gemm_args& a = *ap;
   FITB200_CHECK_ARG(a.A && a.B && a.out && a.M > 0 && a.N > 0 && a.K > 0, "gemm_f32: bad arguments");
-  FITB200_CHECK_ARG(a.K % 4 == 0 && a.lda % 4 == 0 && a.ldb % 4 == 0, "gemm_f32: K, lda, ldb must be multiples of 4 (K=%d)", a.K);
+  FITB200_CHECK_ARG(((a.a_mn && a.b_mn) || a.K % 4 == 0) && (a.a_mn || a.lda % 4 == 0) && (a.b_mn || a.ldb % 4 == 0),
+                    "gemm_f32: K, lda, ldb must be multiples of 4 (K=%d)", a.K);
+  FITB200_CHECK_ARG(!(a.a_mn || a.b_mn) || a.epilogue == FITB200_EPI_BIAS, "gemm_f32: a_mn / b_mn support FITB200_EPI_BIAS only");
   if (a.epilogue == FITB200_EPI_SWIGLU) FITB200_CHECK_ARG(a.B2, "gemm_f32: SWIGLU needs B2");
   if (a.epilogue == FITB200_EPI_BIAS_GATE_RESID)
     FITB200_CHECK_ARG(a.gate && a.resid && a.rows_per_sample > 0, "gemm_f32: GATE_RESID needs gate, resid, rows_per_sample");

@@ -52,7 +52,9 @@ __device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
 }
 
 // OutT = bf16: a slab is 64 output columns; OutT = float: 32 output columns (both 128 bytes per row).
-template <int BN, int EPI, typename OutT>
+// AMN / BMN: the operand is stored contraction-major ([K, M] resp. [K, N] row-major: the dgrad / wgrad GEMMs of the backward pass);
+// its k-slab is fetched as 64-column TMA boxes and read through MN-major SWIZZLE_128B descriptors (tools/probe/umma_probe_mn.cu).
+template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false>
 __global__ void __launch_bounds__(GT_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GtParams p) {
@@ -118,8 +120,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-          ptx::tma_load_2d(smemA + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * GT_BK, m0);
-          ptx::tma_load_2d(smemB + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * GT_BK, n0);
+          if (AMN) {
+#pragma unroll
+            for (int b = 0; b < GT_BM / 64; ++b) ptx::tma_load_2d(smemA + stage * Cfg::A_BYTES + b * 8192, &tmA, &full_bar[stage], m0 + b * 64, kb * GT_BK);
+          } else {
+            ptx::tma_load_2d(smemA + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * GT_BK, m0);
+          }
+          if (BMN) {
+#pragma unroll
+            for (int b = 0; b < BN / 64; ++b) ptx::tma_load_2d(smemB + stage * Cfg::B_BYTES + b * 8192, &tmB, &full_bar[stage], n0 + b * 64, kb * GT_BK);
+          } else {
+            ptx::tma_load_2d(smemB + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * GT_BK, n0);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -128,7 +140,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::idesc_bf16_f32(GT_BM, BN);
+      constexpr uint32_t idesc = ptx::idesc_bf16_f32(GT_BM, BN) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
@@ -139,12 +151,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          const uint64_t da = ptx::smem_desc_kmajor_sw128(ptx::smem_u32(smemA + stage * Cfg::A_BYTES));
-          const uint64_t db = ptx::smem_desc_kmajor_sw128(ptx::smem_u32(smemB + stage * Cfg::B_BYTES));
+          const uint32_t a_addr = ptx::smem_u32(smemA + stage * Cfg::A_BYTES), b_addr = ptx::smem_u32(smemB + stage * Cfg::B_BYTES);
+          const uint64_t da = AMN ? ptx::smem_desc_mnmajor_sw128(a_addr) : ptx::smem_desc_kmajor_sw128(a_addr);
+          const uint64_t db = BMN ? ptx::smem_desc_mnmajor_sw128(b_addr) : ptx::smem_desc_kmajor_sw128(b_addr);
 #pragma unroll
           for (int k = 0; k < GT_BK / 16; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-            ptx::mma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            // 16 elements along K: K-major = 32 bytes inside the 128-byte swizzle row (+2 in the addr >> 4 field);
+            // MN-major = 16 k-rows of 128 bytes (+128)
+            ptx::mma_f16_ss(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0);
           }
           ptx::mma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -348,13 +362,13 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int dtype, long rows, long
   return FITB200_OK;
 }
 
-template <int BN, int EPI, typename OutT>
+template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false>
 static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   using Cfg = GtCfg<BN, EPI>;
   CUtensorMap tmA, tmB, tmOut, tmRes;
-  int rc = make_tmap(&tmA, a.A, FITB200_BF16, a.M, a.K, a.lda, GT_BM, GT_BK);
+  int rc = AMN ? make_tmap(&tmA, a.A, FITB200_BF16, a.K, a.M, a.lda, GT_BK, 64) : make_tmap(&tmA, a.A, FITB200_BF16, a.M, a.K, a.lda, GT_BM, GT_BK);
   if (rc) return rc;
-  rc = make_tmap(&tmB, a.B, FITB200_BF16, a.N, a.K, a.ldb, BN, GT_BK);
+  rc = BMN ? make_tmap(&tmB, a.B, FITB200_BF16, a.K, a.N, a.ldb, GT_BK, 64) : make_tmap(&tmB, a.B, FITB200_BF16, a.N, a.K, a.ldb, BN, GT_BK);
   if (rc) return rc;
   const int outc = 128 / (int)sizeof(OutT);
   const long n_out = EPI == FITB200_EPI_SWIGLU ? a.N / 2 : a.N;
@@ -369,7 +383,7 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   p.M = a.M; p.N = a.N; p.K = a.K; p.bias = a.bias;
   p.gate = a.gate; p.ld_gate = a.ld_gate; p.rows_per_sample = a.rows_per_sample;
   p.rope_freqs = a.rope_freqs; p.rope_rows = a.rope_rows; p.rope_tokens = a.rope_tokens; p.rope_hd = a.rope_head_dim; p.rope_cols = a.rope_cols;
-  auto kern = gemm_tc_kernel<BN, EPI, OutT>;
+  auto kern = gemm_tc_kernel<BN, EPI, OutT, AMN, BMN>;
   static bool attr_done = false;  // per template instantiation
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -385,6 +399,12 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
 
 template <int BN, typename OutT>
 static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
+  if (a.a_mn || a.b_mn) {  // backward GEMMs: plain (optional bias) epilogue only
+    if (a.epilogue != FITB200_EPI_BIAS) { set_last_error("gemm_bf16_tc: a_mn / b_mn support FITB200_EPI_BIAS only"); return FITB200_ERR_UNSUPPORTED; }
+    if (a.a_mn && a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, true>(a, s);
+    if (a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, true>(a, s);
+    return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, false>(a, s);
+  }
   switch (a.epilogue) {
     case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT>(a, s);
     case FITB200_EPI_BIAS_SILU: return launch_tc<BN, FITB200_EPI_BIAS_SILU, OutT>(a, s);
@@ -421,7 +441,8 @@ extern "C" int fitb200_gemm_bf16_tc(const fitb200_gemm_args* ap, fitb200_stream_
   FITB200_CHECK_ARG(ap, "gemm_bf16_tc: null args");
   const fitb200_gemm_args& a = *ap;
   FITB200_CHECK_ARG(a.A && a.B && a.out && a.M > 0 && a.N > 0 && a.K > 0, "gemm_bf16_tc: bad arguments");
-  FITB200_CHECK_ARG(a.K % 8 == 0 && a.lda % 8 == 0 && a.ldb % 8 == 0, "gemm_bf16_tc: K, lda, ldb must be multiples of 8 (K=%d lda=%lld ldb=%lld)", a.K, (long long)a.lda, (long long)a.ldb);
+  FITB200_CHECK_ARG((a.K % 8 == 0 || (a.a_mn && a.b_mn)) && a.lda % 8 == 0 && a.ldb % 8 == 0, "gemm_bf16_tc: K, lda, ldb must be multiples of 8 (K=%d lda=%lld ldb=%lld)", a.K, (long long)a.lda, (long long)a.ldb);
+  FITB200_CHECK_ARG(!a.a_mn || a.M % 8 == 0, "gemm_bf16_tc: a_mn needs M %% 8 == 0 (M=%d)", a.M);
   FITB200_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.B & 15) == 0 && ((uintptr_t)a.out & 15) == 0, "gemm_bf16_tc: A, B, out must be 16-byte aligned");
   FITB200_CHECK_ARG(a.N % 8 == 0 && a.ldo % 8 == 0, "gemm_bf16_tc: N and ldo must be multiples of 8 (N=%d)", a.N);
   FITB200_CHECK_ARG(a.bias == nullptr || ((uintptr_t)a.bias & 15) == 0, "gemm_bf16_tc: bias must be 16-byte aligned");

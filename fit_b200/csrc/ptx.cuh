@@ -124,6 +124,18 @@ __device__ __forceinline__ uint64_t smem_desc_kmajor_sw128(uint32_t smem_addr) {
   return d;
 }
 
+// MN-major operand tile written by TMA with 128-byte swizzle as 64-column boxes: k-row kk of a box at kk * 128 bytes; 8-row groups of
+// 1024 B => SBO = 1024; the next 64 MN elements are the next box, 64 k-rows x 128 B later => LBO = 8192.
+__device__ __forceinline__ uint64_t smem_desc_mnmajor_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(8192 >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
 // Instruction descriptor, kind::f16 (cute::UMMA::InstrDescriptor): D = f32, A = B = bf16, both K-major.
 __host__ __device__ constexpr uint32_t idesc_bf16_f32(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

@@ -65,14 +65,16 @@ def cond_combine(t_emb: Tensor, y: Tensor, table: Tensor, c: Optional[Tensor], s
 def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: int = EPI_BIAS, *, M: Optional[int] = None,
          B2: Optional[Tensor] = None, bias2: Optional[Tensor] = None, gate: Optional[Tensor] = None, ld_gate: int = 0,
          rows_per_sample: int = 1, resid: Optional[Tensor] = None, N: Optional[int] = None,
-         rope: Optional[Tensor] = None, rope_cols: int = 0):
+         rope: Optional[Tensor] = None, rope_cols: int = 0, a_mn: bool = False, b_mn: bool = False, K: Optional[int] = None):
     """out = epilogue(A @ B^T).  A [M,K] and B [N,K] both fp32 (CUDA-core path) or both bf16 (tcgen05 path).
     ``gate`` may be a strided view: pass the storage-offset view and its row stride ``ld_gate``."""
     L.require_cuda(A, B, out)
     a = L.GemmArgs()
-    a.M = A.shape[0] if M is None else M
-    a.K = A.shape[1]
-    a.N = B.shape[0] if N is None else N
+    # a_mn / b_mn: the operand is stored contraction-major, [K, M] resp. [K, N] (backward GEMMs)
+    a.M = (A.shape[1] if a_mn else A.shape[0]) if M is None else M
+    a.K = (A.shape[0] if a_mn else A.shape[1]) if K is None else K
+    a.N = (B.shape[1] if b_mn else B.shape[0]) if N is None else N
+    a.a_mn, a.b_mn = int(a_mn), int(b_mn)
     a.A, a.lda = A.data_ptr(), A.stride(0)
     a.B, a.ldb = B.data_ptr(), B.stride(0)
     a.B2 = 0 if B2 is None else B2.data_ptr()

@@ -89,6 +89,12 @@ typedef struct {
    * n % rope_head_dim; the pair (2j, 2j+1) is rotated by (cos, sin) = rope_freqs[(s or 0), token, 2j .. 2j+1]
    * (fp32 [rope_rows = 1 | samples, rope_tokens, rope_head_dim], the table of pos_embed.py:51-75). */
   const float* rope_freqs; int32_t rope_rows, rope_tokens, rope_head_dim, rope_cols;
+  /* Backward GEMMs (autograd of nn.Linear, FiT/train.py:55-66): a_mn = 1: A is stored [K, M] row-major (lda = its row stride);
+   * b_mn = 1: B is stored [K, N] row-major.  out[m,n] = sum_k A(m,k) B(n,k) in every case.
+   *   dgrad  dX[M,K'] = dY[M,N] W[N,K']   : A = dY,  B = W  with b_mn = 1 (no transposed weight copy)
+   *   wgrad  dW[N,K'] = dY[M,N]^T X[M,K'] : A = dY with a_mn = 1, B = X with b_mn = 1 (contraction over the token rows)
+   * FITB200_EPI_BIAS (bias may be NULL) only. */
+  int32_t a_mn, b_mn;
 } fitb200_gemm_args;
 
 /* fp32 FMA GEMM on CUDA cores: A, B, B2 fp32.  The fp32 verification mode and the small

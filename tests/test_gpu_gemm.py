@@ -151,3 +151,29 @@ def test_gemm_qkv_rope_epilogue(ops, odt, R, T, h, d, rows):
     tol = 1e-5 if odt == torch.float32 else 4e-3
     assert rel_l2(out.float(), want) < tol
     assert rel_l2(out.float()[:, 2 * D:], want[:, 2 * D:]) < tol
+
+
+@pytest.mark.parametrize("wdt,odt", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16), (torch.bfloat16, torch.float32)])
+@pytest.mark.parametrize("M,N,K", [(256, 1152, 3456), (200, 768, 2048), (1000, 3072, 1152), (512, 128, 64), (136, 2736, 1024)])
+def test_gemm_dgrad_b_mn(ops, wdt, odt, M, N, K):
+    """dX[M,N] = dY[M,K] W[K,N]: the weight is read in its nn.Linear layout through b_mn (no transposed copy)."""
+    g = torch.Generator().manual_seed(M + N)
+    dY = torch.randn(M, K, generator=g).to(wdt)
+    W = (torch.randn(K, N, generator=g) / K ** 0.5).to(wdt)
+    want = dY.double() @ W.double()
+    out = torch.empty(M, N, dtype=odt, device="cuda")
+    ops.gemm(dY.cuda(), W.cuda(), None, out, EPI_BIAS, b_mn=True)
+    assert rel_l2(out.float(), want) < (1e-5 if odt == torch.float32 else 4e-3)
+
+
+@pytest.mark.parametrize("wdt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,N,K", [(512, 1152, 1152), (400, 3456, 768), (8192, 256, 128), (77 * 8, 2736, 1024), (200, 16, 768)])
+def test_gemm_wgrad_ab_mn(ops, wdt, rows, N, K):
+    """dW[N,K] = dY[rows,N]^T X[rows,K]: both operands contraction-major (a_mn, b_mn), contraction over the token rows, fp32 out."""
+    g = torch.Generator().manual_seed(rows + N)
+    dY = torch.randn(rows, N, generator=g).to(wdt)
+    X = torch.randn(rows, K, generator=g).to(wdt)
+    want = dY.double().t() @ X.double()
+    out = torch.empty(N, K, dtype=torch.float32, device="cuda")
+    ops.gemm(dY.cuda(), X.cuda(), None, out, EPI_BIAS, a_mn=True, b_mn=True)
+    assert rel_l2(out, want) < 1e-5

@@ -38,7 +38,8 @@ def test_gemm_args_struct_matches_header_layout():
     assert GemmArgs.out_dtype.offset == 88 and GemmArgs.epilogue.offset == 92 and GemmArgs.gate.offset == 96
     assert GemmArgs.rows_per_sample.offset == 112 and GemmArgs.resid.offset == 120 and GemmArgs.resid_dtype.offset == 136
     assert GemmArgs.rope_freqs.offset == 144 and GemmArgs.rope_rows.offset == 152 and GemmArgs.rope_cols.offset == 164
-    assert ctypes.sizeof(GemmArgs) == 168
+    assert GemmArgs.a_mn.offset == 168 and GemmArgs.b_mn.offset == 172
+    assert ctypes.sizeof(GemmArgs) == 176
 
 
 @pytest.mark.parametrize("rs", ["10", "250", "ddim25", ""])
