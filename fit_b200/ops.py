@@ -215,3 +215,97 @@ def gather_i64(table: Tensor, idx: Tensor, out: Tensor):
 def add_i64(idx: Tensor, delta: int):
     L.check(L.lib().fitb200_add_i64(L.ptr(idx), idx.shape[0], int(delta), L.stream_ptr()), "add_i64")
     return idx
+
+
+# ---------------------------------------------------------------------------------------------- training step (backward.cu, attn_bwd.cu)
+def _m8(mask):
+    return None if mask is None else _c(mask.view(torch.uint8) if mask.dtype == torch.bool else mask)
+
+
+def attention_bwd(qkv: Tensor, freqs: Tensor, kv_len: Tensor, mask: Optional[Tensor], R: int, T: int, h: int, d: int, out: Tensor,
+                  dout: Tensor, lse: Tensor, dqkv: Tensor, prerotated: bool = False):
+    """Gradient of attention() with respect to the un-rotated q, k and v: dqkv [R*T, 3*h*d]."""
+    L.require_cuda(qkv, freqs, kv_len, out, dout, lse, dqkv)
+    assert freqs.dtype == torch.float32 and lse.dtype == torch.float32 and qkv.dtype == out.dtype == dout.dtype == dqkv.dtype
+    fr = 1 if freqs.dim() == 2 else freqs.shape[0]
+    L.check(L.lib().fitb200_attn_bwd(L.ptr(_c(qkv)), L.dtype_code(qkv), L.ptr(_c(freqs)), fr, L.ptr(kv_len), L.ptr(_m8(mask)), R, T, h, d,
+                                     int(prerotated), L.ptr(_c(out)), L.ptr(_c(dout)), L.ptr(lse), L.ptr(dqkv), L.stream_ptr()), "attn_bwd")
+    return dqkv
+
+
+def gate_resid_fwd(resid: Tensor, y: Tensor, gate: Tensor, ld_gate: int, rows_per_sample: int, out: Tensor):
+    M, D = resid.shape
+    L.check(L.lib().fitb200_gate_resid_fwd(L.ptr(_c(resid)), L.ptr(_c(y)), L.dtype_code(resid), L.ptr(gate), ld_gate, M, D, rows_per_sample,
+                                           L.ptr(out), L.stream_ptr()), "gate_resid_fwd")
+    return out
+
+
+def gate_bwd(dx: Tensor, y: Tensor, gate: Tensor, ld_gate: int, R: int, rows_per_sample: int, dy: Tensor, dgate: Tensor, ld_dgate: int,
+             dbias: Optional[Tensor]):
+    D = dx.shape[1]
+    L.check(L.lib().fitb200_gate_bwd(L.ptr(_c(dx)), L.ptr(_c(y)), L.dtype_code(dx), L.ptr(gate), ld_gate, R, rows_per_sample, D, L.ptr(dy),
+                                     L.ptr(dgate), ld_dgate, L.ptr(dbias), L.stream_ptr()), "gate_bwd")
+    return dy
+
+
+def swiglu_fwd(u: Tensor, g: Tensor):
+    M, Hp = g.shape
+    L.check(L.lib().fitb200_swiglu_fwd(L.ptr(_c(u)), L.dtype_code(u), M, Hp, L.ptr(g), L.stream_ptr()), "swiglu_fwd")
+    return g
+
+
+def swiglu_bwd(dg: Tensor, u: Tensor, du: Tensor, dbias: Optional[Tensor]):
+    M, Hp = dg.shape
+    L.check(L.lib().fitb200_swiglu_bwd(L.ptr(_c(dg)), L.ptr(_c(u)), L.dtype_code(u), M, Hp, L.ptr(du), L.ptr(dbias), L.stream_ptr()), "swiglu_bwd")
+    return du
+
+
+def ln_modulate_bwd(dh: Tensor, x: Tensor, mean: Tensor, rstd: Tensor, scale: Tensor, ld_mod: int, rows_per_sample: int,
+                    dres: Optional[Tensor], dx: Tensor, dshift: Optional[Tensor], dscale: Optional[Tensor], ld_dmod: int):
+    M, D = x.shape
+    L.check(L.lib().fitb200_ln_modulate_bwd(L.ptr(_c(dh)), L.ptr(_c(x)), L.dtype_code(x), L.ptr(mean), L.ptr(rstd), L.ptr(scale), ld_mod, M, D,
+                                            rows_per_sample, L.ptr(dres), L.ptr(dx), L.ptr(dshift), L.ptr(dscale), ld_dmod, L.stream_ptr()),
+            "ln_modulate_bwd")
+    return dx
+
+
+def colsum(a: Tensor, out: Tensor):
+    """out[n] += sum_m a[m, n] (out fp32, zero-initialised by the caller)."""
+    M, N = a.shape
+    L.check(L.lib().fitb200_colsum(L.ptr(a), L.dtype_code(a), M, N, a.stride(0), L.ptr(out), L.stream_ptr()), "colsum")
+    return out
+
+
+def silu_fwd(x: Tensor, y: Tensor):
+    L.check(L.lib().fitb200_silu_fwd(L.ptr(_c(x)), x.numel(), L.ptr(y), L.stream_ptr()), "silu_fwd")
+    return y
+
+
+def silu_bwd(dy: Tensor, x: Tensor, dx: Tensor):
+    L.check(L.lib().fitb200_silu_bwd(L.ptr(_c(dy)), L.ptr(_c(x)), x.numel(), L.ptr(dx), L.stream_ptr()), "silu_bwd")
+    return dx
+
+
+def embedding_bwd(dc: Tensor, y: Tensor, dtable: Tensor):
+    R, D = dc.shape
+    L.check(L.lib().fitb200_embedding_bwd(L.ptr(_c(dc)), L.ptr(_c(y)), R, D, dtable.shape[0], L.ptr(dtable), L.stream_ptr()), "embedding_bwd")
+    return dtable
+
+
+def cast(src: Tensor, dst: Tensor):
+    L.check(L.lib().fitb200_cast(L.ptr(_c(src)), L.dtype_code(src), L.ptr(dst), L.dtype_code(dst), src.numel(), L.stream_ptr()), "cast")
+    return dst
+
+
+def masked_mse_fwd(out: Tensor, target: Tensor, mask: Tensor, acc: Tensor, loss: Tensor):
+    P = out.shape[-1]
+    L.check(L.lib().fitb200_masked_mse_fwd(L.ptr(_c(out)), L.ptr(_c(target)), L.ptr(_m8(mask)), mask.numel(), P, L.ptr(acc), L.ptr(loss),
+                                           L.stream_ptr()), "masked_mse_fwd")
+    return loss
+
+
+def masked_mse_bwd(out: Tensor, target: Tensor, mask: Tensor, acc: Tensor, gscale: Optional[Tensor], dout: Tensor):
+    P = out.shape[-1]
+    L.check(L.lib().fitb200_masked_mse_bwd(L.ptr(_c(out)), L.ptr(_c(target)), L.ptr(_m8(mask)), mask.numel(), P, L.ptr(acc), L.ptr(gscale),
+                                           L.ptr(dout), L.dtype_code(dout), L.stream_ptr()), "masked_mse_bwd")
+    return dout

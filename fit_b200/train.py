@@ -1,16 +1,147 @@
-"""Training-step arithmetic of the hot path (FiT/train.py:45-69): autograd bridge + masked MSE.  (backward kernels: WIP)"""
+"""Training-step arithmetic of the hot path (FiT/train.py:45-69, masked_FiT/train.py:40-60): the autograd bridge that makes
+``loss.backward()`` run the hand-written backward, the masked MSE, q_sample (= DDIMScheduler.add_noise) and the data-parallel
+gradient exchange (DDP-style NCCL all-reduce, bucketed per block and overlapped with the rest of the backward)."""
 from __future__ import annotations
+
+from typing import Dict, List, Optional
 
 import torch
 
+from . import ops
+from .engine_train import FiTTrainEngine
+
+Tensor = torch.Tensor
+BACKWARD_READY = True
+
+
+def _train_engine(model) -> FiTTrainEngine:
+    eng = getattr(model, "_train_engine", None)
+    if eng is None or eng.precision != model.precision:
+        eng = FiTTrainEngine(model, model.precision)
+        object.__setattr__(model, "_train_engine", eng)
+    return eng
+
+
+class _FiTFunction(torch.autograd.Function):
+    """One autograd node for the whole network: forward keeps the activations, backward returns every parameter gradient."""
+
+    @staticmethod
+    def forward(ctx, model, x, t, y, pos, mask, train, *params):
+        eng = _train_engine(model)
+        out, saved = eng.forward(x, t, y, pos, mask, train)
+        ctx.eng, ctx.saved, ctx.names = eng, saved, [n for n, _ in model.named_parameters()]
+        ctx.sync = getattr(model, "_grad_sync", None)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        sync = ctx.sync
+        grads = ctx.eng.backward(ctx.saved, dout.contiguous(), on_grads=None if sync is None else sync.on_grads)
+        if sync is not None:
+            sync.finish()
+        ctx.saved = None
+        return (None,) * 7 + tuple(grads.get(n) for n in ctx.names)
+
 
 def fit_forward_autograd(model, x, t, y, pos, mask, train=True):
-    raise NotImplementedError("fit_b200: backward kernels not built yet")
+    """FiT.forward under autograd (called by fit_b200.models.fit.FiT.forward when gradients are required)."""
+    y = model.y_embedder.labels_for(y, model.training)
+    return _FiTFunction.apply(model, x, t, y, pos, mask, train, *model.parameters())
 
 
-def masked_mse_loss(out, target, mask):
-    raise NotImplementedError("fit_b200: backward kernels not built yet")
+class _MaskedMSE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, out, target, mask):
+        acc = torch.zeros(2, dtype=torch.float32, device=out.device)
+        loss = torch.empty(1, dtype=torch.float32, device=out.device)
+        out_c, target_c = out.float().contiguous(), target.float().contiguous()
+        ops.masked_mse_fwd(out_c, target_c, mask, acc, loss)
+        ctx.save_for_backward(out_c, target_c, mask, acc)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        out, target, mask, acc = ctx.saved_tensors
+        dout = torch.empty_like(out)
+        ops.masked_mse_bwd(out, target, mask, acc, g.reshape(1).float().contiguous(), dout)
+        return dout, None, None
 
 
-def masked_token_mse(out, target, mask):
-    raise NotImplementedError("fit_b200: backward kernels not built yet")
+def masked_mse_loss(out: Tensor, target: Tensor, mask: Tensor) -> Tensor:
+    """F.mse_loss(out[mask], target[mask]) of FiT/train.py:63-66 (tokens [N, T, P], mask [N, T] bool) as one fused kernel each way."""
+    if not out.is_cuda:
+        raise RuntimeError("fit_b200 kernels need CUDA tensors (there is no CPU fallback)")
+    return _MaskedMSE.apply(out, target, mask)
+
+
+masked_token_mse = masked_mse_loss
+
+
+def add_noise(diffusion, x0: Tensor, noise: Tensor, t: Tensor) -> Tensor:
+    """DDIMScheduler(num_train_timesteps=1000).add_noise call site (FiT/train.py:53) = q_sample with the linear schedule."""
+    return diffusion.q_sample(x0, t, noise=noise)
+
+
+# ---------------------------------------------------------------------------------------------------- data parallel
+class GradSync:
+    """DDP-style gradient averaging for the custom backward.
+
+    The backward hands over each block's parameter gradients as soon as they are final (``on_grads``); they are packed into one
+    flat fp32 bucket per block and all-reduced (NCCL over NVLink / NVSwitch on GPUs, gloo in the CPU tests) on a side stream
+    while the backward of the earlier blocks keeps the compute stream busy.  ``finish`` joins the side stream, scales by
+    1 / world_size and scatters the averaged values back into the gradient tensors autograd returns.
+    ``no_sync`` skips the exchange on non-final accumulation micro-steps (accumulate_grad_batches=2, FiT/train.py:288)."""
+
+    def __init__(self, process_group=None, bucket_bytes: int = 0):
+        import torch.distributed as dist
+        self.dist, self.pg = dist, process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.enabled = True
+        self._pending: List = []
+        self._stream = None
+
+    def attach(self, model):
+        object.__setattr__(model, "_grad_sync", self)
+        return self
+
+    class _NoSync:
+        def __init__(self, gs): self.gs = gs
+        def __enter__(self): self.gs.enabled = False
+        def __exit__(self, *a): self.gs.enabled = True
+
+    def no_sync(self):
+        return GradSync._NoSync(self)
+
+    def on_grads(self, tag: str, grads: Dict[str, Tensor]):
+        if not self.enabled or self.world == 1:
+            return
+        tensors = list(grads.values())
+        flat = torch.cat([g.reshape(-1) for g in tensors])   # packing copy (no arithmetic)
+        if flat.is_cuda:
+            if self._stream is None:
+                self._stream = torch.cuda.Stream(device=flat.device)
+            ready = torch.cuda.current_stream().record_event()
+            self._stream.wait_event(ready)
+            with torch.cuda.stream(self._stream):
+                work = self.dist.all_reduce(flat, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True)
+            flat.record_stream(self._stream)
+        else:
+            work = self.dist.all_reduce(flat, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True)
+        self._pending.append((flat, tensors, work))
+
+    def finish(self):
+        if not self._pending:
+            return
+        for flat, tensors, work in self._pending:
+            work.wait()
+        if self._stream is not None:
+            torch.cuda.current_stream().wait_stream(self._stream)
+        inv = 1.0 / self.world
+        for flat, tensors, _ in self._pending:
+            flat.mul_(inv)   # the mean of DDP; elementwise scale of the reduced bucket
+            off = 0
+            for g in tensors:
+                n = g.numel()
+                g.copy_(flat[off:off + n].view_as(g))
+                off += n
+        self._pending.clear()

@@ -132,6 +132,15 @@ int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, int freqs_r
                      const uint8_t* mask, int R, int T, int h, int d, int flags, void* out, float* lse,
                      fitb200_stream_t stream);
 
+/* Backward of the above (autograd of fit.py:160-188 as triggered by loss.backward(), FiT/train.py:55-66).
+ * qkv / flags / freqs / kv_len / mask exactly as given to the forward; out = the forward's output [R, T, h*d], dout its gradient,
+ * lse the forward's log-sum-exp.  dqkv [R, T, 3, h, d] receives the gradient with respect to the UN-rotated q, k (and v): the
+ * RoPE's transpose (rotation by -theta) is applied in the kernel, so dqkv feeds the qkv Linear's dgrad / wgrad directly.
+ * Rows of padded tokens are written as zeros.  CUDA-core kernel (exact fp32 math; bf16 storage supported). */
+int fitb200_attn_bwd(const void* qkv, int dtype, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask,
+                     int R, int T, int h, int d, int flags, const void* out, const void* dout, const float* lse, void* dqkv,
+                     fitb200_stream_t stream);
+
 /* ---- final layer ---------------------------------------------------------------------------------
  * FinalLayer.forward (dit.py:138-142) after its adaLN Linear: LN + modulate + Linear(D -> P) with
  * P = p*p*C_out, optionally fused with FiT.unpatchify (fit.py:444-456).
@@ -190,6 +199,43 @@ int fitb200_philox_normal(float* out, int rows, int64_t per_row, uint64_t seed, 
  * out[i] = map[clamp(idx[i])]; and idx[i] += delta. */
 int fitb200_gather_i64(const int64_t* map, int map_len, const int64_t* idx, int64_t* out, int n, fitb200_stream_t stream);
 int fitb200_add_i64(int64_t* idx, int n, int64_t delta, fitb200_stream_t stream);
+
+/* ==== training step: un-fused forward pieces + backward kernels =====================================================
+ * Autograd of FiTBlock.forward (fit.py:326-337) and of the training-step arithmetic (FiT/train.py:45-69).  "act dtype" tensors
+ * are bf16 or fp32; reductions, modulation tables and parameter gradients are fp32.  Buffers marked "+=" are accumulated with
+ * atomics and must be zero-initialised by the caller. */
+
+/* out = resid + gate[m / rows_per_sample] * y   (x + gate * branch, fit.py:331,337; the training forward keeps y) */
+int fitb200_gate_resid_fwd(const void* resid, const void* y, int dtype, const float* gate, int64_t ld_gate, int M, int D,
+                           int rows_per_sample, void* out, fitb200_stream_t stream);
+/* dy = gate[s] * dx;  dgate[s,:] += sum_t dx * y;  dbias[:] += column sums of dy (nullable) */
+int fitb200_gate_bwd(const void* dx, const void* y, int dtype, const float* gate, int64_t ld_gate, int R, int rows_per_sample, int D,
+                     void* dy, float* dgate, int64_t ld_dgate, float* dbias, fitb200_stream_t stream);
+/* SwiGLU gating (fit.py:278-280) on the packed pre-activations u [M, 2*Hp] (16 gate columns then the matching 16 up columns,
+ * the layout of the packed fc1 weight):  g = silu(u_gate) * u_up;  backward: du (same layout), dbias[2*Hp] += column sums */
+int fitb200_swiglu_fwd(const void* u, int dtype, int M, int Hp, void* g, fitb200_stream_t stream);
+int fitb200_swiglu_bwd(const void* dg, const void* u, int dtype, int M, int Hp, void* du, float* dbias, fitb200_stream_t stream);
+/* modulate(LayerNorm(x)) backward (fit.py:45-46,303,332,336): dx = dres (nullable) + LN^T(dh * (1 + scale[s]));
+ * dshift[s,:] += sum_t dh;  dscale[s,:] += sum_t dh * xhat  (both nullable together).  mean / rstd from the forward. */
+int fitb200_ln_modulate_bwd(const void* dh, const void* x, int dtype, const float* mean, const float* rstd, const float* scale,
+                            int64_t ld_mod, int M, int D, int rows_per_sample, const void* dres, void* dx, float* dshift, float* dscale,
+                            int64_t ld_dmod, fitb200_stream_t stream);
+/* out[n] += sum_m a[m, n]   (bias gradients) */
+int fitb200_colsum(const void* a, int dtype, int M, int N, int64_t lda, float* out, fitb200_stream_t stream);
+/* y = silu(x);  dx = dy * silu'(x)   (t-embedder MLP fit.py:55-57, adaLN SiLU fit.py:323) */
+int fitb200_silu_fwd(const float* x, int64_t n, float* y, fitb200_stream_t stream);
+int fitb200_silu_bwd(const float* dy, const float* x, int64_t n, float* dx, fitb200_stream_t stream);
+/* dtable[y[r], :] += dc[r, :]   (LabelEmbedder, fit.py:114) */
+int fitb200_embedding_bwd(const float* dc, const int64_t* y, int R, int D, int table_rows, float* dtable, fitb200_stream_t stream);
+/* dst = (dst dtype) src */
+int fitb200_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, fitb200_stream_t stream);
+/* F.mse_loss(out[mask], target[mask]) (FiT/train.py:63-66): out / target fp32 [tokens, P], mask bytes [tokens].
+ * fwd: acc[0] += sum of squared errors over valid tokens, acc[1] += number of valid tokens (acc zeroed by the caller),
+ *      loss[0] = acc[0] / (acc[1] * P).   bwd: dout = gscale[0] (nullable = 1) * 2 (out - target) mask / (acc[1] * P). */
+int fitb200_masked_mse_fwd(const float* out, const float* target, const uint8_t* mask, int64_t tokens, int P, float* acc, float* loss,
+                           fitb200_stream_t stream);
+int fitb200_masked_mse_bwd(const float* out, const float* target, const uint8_t* mask, int64_t tokens, int P, const float* acc,
+                           const float* gscale, void* dout, int dout_dtype, fitb200_stream_t stream);
 
 #ifdef __cplusplus
 }
