@@ -13,6 +13,9 @@
 
 namespace fitb200 {
 
+int attn_bwd_tc(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d,
+                const void* o, const void* dO, const float* lse, void* dqkv, cudaStream_t s);
+
 constexpr int AB_T = 32;         // tile edge
 constexpr int AB_THREADS = 256;
 constexpr int AB_QSKIP = 128;    // the forward skips (zero-fills) query tiles of 128 starting at or beyond kv_len
@@ -208,6 +211,10 @@ extern "C" int fitb200_attn_bwd(const void* qkv, int dtype, const float* freqs, 
   FITB200_CHECK_ARG(h <= 65535 && R <= 65535, "attn_bwd: h and R must be <= 65535");
   const int pre = flags & FITB200_ATTN_PREROTATED;
   cudaStream_t s = (cudaStream_t)stream;
+  // bf16 training path (pre-rotated operands, trained sequence lengths): tcgen05 kernel; everything else: CUDA cores
+  if (dtype == FITB200_BF16 && pre && T <= 256 && (d == 64 || d == 72) && !(flags & FITB200_ATTN_FORCE_SIMT) &&
+      ((uintptr_t)qkv & 15) == 0 && ((uintptr_t)dout & 15) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)dqkv & 15) == 0)
+    return attn_bwd_tc(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, d, out, dout, lse, dqkv, s);
   FITB200_DISPATCH_ACT(dtype, AT, {
     if (d == 64) return launch_attn_bwd<64, AT>(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, pre, out, dout, lse, dqkv, s);
     if (d == 72) return launch_attn_bwd<72, AT>(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, pre, out, dout, lse, dqkv, s);

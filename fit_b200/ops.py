@@ -223,13 +223,14 @@ def _m8(mask):
 
 
 def attention_bwd(qkv: Tensor, freqs: Tensor, kv_len: Tensor, mask: Optional[Tensor], R: int, T: int, h: int, d: int, out: Tensor,
-                  dout: Tensor, lse: Tensor, dqkv: Tensor, prerotated: bool = False):
+                  dout: Tensor, lse: Tensor, dqkv: Tensor, prerotated: bool = False, force_simt: bool = False):
     """Gradient of attention() with respect to the un-rotated q, k and v: dqkv [R*T, 3*h*d]."""
     L.require_cuda(qkv, freqs, kv_len, out, dout, lse, dqkv)
     assert freqs.dtype == torch.float32 and lse.dtype == torch.float32 and qkv.dtype == out.dtype == dout.dtype == dqkv.dtype
     fr = 1 if freqs.dim() == 2 else freqs.shape[0]
     L.check(L.lib().fitb200_attn_bwd(L.ptr(_c(qkv)), L.dtype_code(qkv), L.ptr(_c(freqs)), fr, L.ptr(kv_len), L.ptr(_m8(mask)), R, T, h, d,
-                                     int(prerotated), L.ptr(_c(out)), L.ptr(_c(dout)), L.ptr(lse), L.ptr(dqkv), L.stream_ptr()), "attn_bwd")
+                                     int(prerotated) | (2 if force_simt else 0), L.ptr(_c(out)), L.ptr(_c(dout)), L.ptr(lse), L.ptr(dqkv),
+                                     L.stream_ptr()), "attn_bwd")
     return dqkv
 
 

@@ -124,3 +124,12 @@ class CFGSampler:
             return self.x.clone()
         out.copy_(self.x, non_blocking=True)
         return out
+
+
+def shard_rows(total: int, world: int, rank: int) -> Tuple[int, int]:
+    """[begin, end) of the images rank `rank` samples when a batch of `total` is sharded over `world` GPUs (no collective:
+    each image's trajectory depends only on its own latent, label and noise).  `begin` is the
+    ``row_offset`` to give CFGSampler so the noise is keyed by the global image index."""
+    base, rem = divmod(total, world)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)

@@ -96,6 +96,8 @@ class GradSync:
         import torch.distributed as dist
         self.dist, self.pg = dist, process_group
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        # NCCL averages inside the collective (ReduceOp.AVG); gloo (CPU tests) sums and the bucket is scaled afterwards
+        self.avg_in_collective = dist.is_initialized() and dist.get_backend(process_group) == "nccl"
         self.enabled = True
         self._pending: List = []
         self._stream = None
@@ -123,7 +125,8 @@ class GradSync:
             ready = torch.cuda.current_stream().record_event()
             self._stream.wait_event(ready)
             with torch.cuda.stream(self._stream):
-                work = self.dist.all_reduce(flat, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True)
+                work = self.dist.all_reduce(flat, op=self.dist.ReduceOp.AVG if self.avg_in_collective else self.dist.ReduceOp.SUM,
+                                            group=self.pg, async_op=True)
             flat.record_stream(self._stream)
         else:
             work = self.dist.all_reduce(flat, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True)
@@ -138,7 +141,8 @@ class GradSync:
             torch.cuda.current_stream().wait_stream(self._stream)
         inv = 1.0 / self.world
         for flat, tensors, _ in self._pending:
-            flat.mul_(inv)   # the mean of DDP; elementwise scale of the reduced bucket
+            if not self.avg_in_collective:
+                flat.mul_(inv)   # gloo has no AVG: scale the reduced bucket (CPU test path only)
             off = 0
             for g in tensors:
                 n = g.numel()

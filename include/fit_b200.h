@@ -127,7 +127,7 @@ int fitb200_ln_modulate_fwd(const void* x, int x_dtype, int M, int D, int rows_p
  * flags: FITB200_ATTN_PREROTATED = q and k in qkv already carry the RoPE (written by a FITB200_EPI_BIAS_ROPE GEMM);
  *        freqs is then ignored (may be NULL).  bf16 only.
  * bf16, T <= 256: tcgen05 / TMEM kernel (attn_tc.cu); bf16, T > 256: chunked mma.sync kernel; fp32: CUDA-core kernel. */
-enum { FITB200_ATTN_PREROTATED = 1 };
+enum { FITB200_ATTN_PREROTATED = 1, FITB200_ATTN_FORCE_SIMT = 2 /* backward only: take the CUDA-core kernel */ };
 int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, int freqs_rows, const int32_t* kv_len,
                      const uint8_t* mask, int R, int T, int h, int d, int flags, void* out, float* lse,
                      fitb200_stream_t stream);
@@ -136,7 +136,8 @@ int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, int freqs_r
  * qkv / flags / freqs / kv_len / mask exactly as given to the forward; out = the forward's output [R, T, h*d], dout its gradient,
  * lse the forward's log-sum-exp.  dqkv [R, T, 3, h, d] receives the gradient with respect to the UN-rotated q, k (and v): the
  * RoPE's transpose (rotation by -theta) is applied in the kernel, so dqkv feeds the qkv Linear's dgrad / wgrad directly.
- * Rows of padded tokens are written as zeros.  CUDA-core kernel (exact fp32 math; bf16 storage supported). */
+ * Rows of padded tokens are written as zeros.  bf16 + PREROTATED + T <= 256: tcgen05 / TMEM kernel (attn_bwd_tc.cu); otherwise the
+ * CUDA-core kernel (exact fp32 math; bf16 storage supported). */
 int fitb200_attn_bwd(const void* qkv, int dtype, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask,
                      int R, int T, int h, int d, int flags, const void* out, const void* dout, const float* lse, void* dqkv,
                      fitb200_stream_t stream);

@@ -142,6 +142,8 @@ def test_masked_mse(ops):
     (96, 3, 72, [96, 10, 33], False),
     (256, 2, 72, [256, 200, 129, 17], False),
     (200, 2, 64, [200, 7], True),
+    (256, 3, 64, [256, 128, 130, 16], False),
+    (8, 1, 72, [8, 3], False),
 ])
 def test_attention_bwd(ops, dt, T, h, d, lens, nonprefix):
     from oracle import fit_oracle as fo
@@ -162,8 +164,9 @@ def test_attention_bwd(ops, dt, T, h, d, lens, nonprefix):
     want = leaf.grad.reshape(R, T, 3 * h * d)
     kv, _ = ops.mask_to_kvlen(mask.cuda())
     tol = 2e-5 if dt == torch.float32 else 1.5e-2
-    variants = [False] if dt == torch.float32 else [False, True]
-    for pre in variants:
+    # (pre-rotated operands, CUDA-core kernel forced): bf16 + pre-rotated defaults to the tcgen05 kernel for T <= 256
+    variants = [(False, False)] if dt == torch.float32 else [(False, False), (True, False), (True, True)]
+    for pre, simt in variants:
         if pre:   # forward operands pre-rotated (the bf16 path); the gradient is still for the un-rotated q, k
             q3, k3, v3 = qkv.permute(2, 0, 3, 1, 4)
             src = torch.stack([fo.rope_rotate(q3, freqs), fo.rope_rotate(k3, freqs), v3], 0).permute(1, 3, 0, 2, 4).contiguous()
@@ -174,11 +177,12 @@ def test_attention_bwd(ops, dt, T, h, d, lens, nonprefix):
         lse = torch.empty(R, h, T, device="cuda")
         ops.attention(src_c, None if pre else freqs.cuda(), kv, mask.cuda(), R, T, h, d, out, lse, prerotated=pre)
         dqkv = torch.full((R * T, 3 * h * d), float("nan"), dtype=dt, device="cuda")
-        ops.attention_bwd(src_c, freqs.cuda(), kv, mask.cuda(), R, T, h, d, out, dO.to(dt).cuda().view(R * T, h * d), lse, dqkv, prerotated=pre)
+        ops.attention_bwd(src_c, freqs.cuda(), kv, mask.cuda(), R, T, h, d, out, dO.to(dt).cuda().view(R * T, h * d), lse, dqkv, prerotated=pre,
+                          force_simt=simt)
         got = dqkv.float().cpu().view(R, T, 3 * h * d)
         assert bool(torch.isfinite(got).all())
         for r, L in enumerate(lens):
-            assert rel_l2(got[r, :L], want[r, :L]) < tol, (pre, r, L)
+            assert rel_l2(got[r, :L], want[r, :L]) < tol, (pre, simt, r, L)
             assert float(got[r, L:].abs().max()) == 0.0 if L < T and not nonprefix else True
 
 
