@@ -1,27 +1,43 @@
-"""Launch each hot kernel of one FiT-XL/2 block once at the headline shape (R=512 rows x 256 tokens) -- the command ncu wraps."""
+"""ncu target: a few FiT-XL/2 blocks at the headline shape (R=512 rows x 256 tokens), forward only, so that
+`ncu --set full -k regex:... -s 9 -c 9` lands on steady-state launches of each block kernel (7 launches per block).
+PROF_TRAIN=1 adds one training step at the config-4 per-GPU shape (32 x 256) for the backward kernels."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from fit_b200.models.fit import FiT
-from fit_b200.rope import precompute_freqs_cis_2d
 import bench
+from fit_b200.models.fit import FiT_models
+from fit_b200.rope import precompute_freqs_cis_2d
 
-R = int(os.environ.get("PROF_ROWS", "512"))
-name = os.environ.get("PROF_MODEL", "FiT-XL/2")
+name = os.environ.get("MODEL", "FiT-XL/2")
+R, T = int(os.environ.get("ROWS", 512)), 256
+D, Hd, L, heads = bench.MODELS[name]
 torch.manual_seed(0)
 with torch.device("cuda"):
-    cfgs = {"FiT-XL/2": dict(hidden_size=1152, num_heads=16), "FiT-B/2": dict(hidden_size=768, num_heads=12)}
-    m = FiT(depth=2, patch_size=2, **cfgs[name])
+    m = FiT_models[name](precision="bf16")
 bench.randomize_zero_init(m)
-m = m.eval()
-dh = m.hidden_size // m.num_heads
-pos = torch.tensor(precompute_freqs_cis_2d(dh, 16, 16, max_length=256), dtype=torch.float32)[None].cuda()
-x = torch.randn(R // 2, 4, 32, 32, device="cuda")
-t = torch.full((R,), 500, device="cuda")
+m.eval()
+d = D // heads
+pos = torch.tensor(precompute_freqs_cis_2d(d, 16, 16, max_length=256), dtype=torch.float32)[None].cuda()
+mask = torch.ones(R, T, dtype=torch.bool, device="cuda")
+x = torch.randn(R, 4, 32, 32, device="cuda")
+t = torch.full((R,), 500, dtype=torch.int64, device="cuda")
 y = torch.randint(0, 1000, (R,), device="cuda")
-mask = torch.ones(R, 256, dtype=torch.bool, device="cuda")
+eng = m.engine
+W = eng.weights()
+ws = eng.workspace(R, T, x.device)
 with torch.no_grad():
-    for _ in range(int(os.environ.get("PROF_ITERS", "2"))):
-        out = m.engine.forward(x, t, y, pos, mask, train=False, rows=R)
-torch.cuda.synchronize()
-print("ok", float(out.float().abs().mean()))
+    m(x, t, y, pos, mask, train=False)          # conditioning + every buffer initialised
+    torch.cuda.synchronize()
+    for i in range(int(os.environ.get("BLOCKS", 4))):
+        eng.block(i, ws, W, pos, mask)
+    torch.cuda.synchronize()
+if os.environ.get("PROF_TRAIN", "0") == "1":
+    from fit_b200.train import masked_mse_loss
+    N = 32
+    m.train(); m.y_embedder.dropout_prob = 0.0
+    xt = torch.randn(N, T, 16, device="cuda"); tgt = torch.randn(N, T, 16, device="cuda")
+    posb = pos.expand(N, T, d).contiguous()
+    out = m(xt, t[:N], y[:N], posb, mask[:N], train=True)
+    masked_mse_loss(out, tgt, mask[:N]).backward()
+    torch.cuda.synchronize()
+print("prof_kernels done")
