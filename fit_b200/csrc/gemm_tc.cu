@@ -25,16 +25,21 @@ constexpr int GT_EPI_THREADS = 256;  // two warps per TMEM lane quarter: each ta
 constexpr int GT_SLAB_BYTES = GT_BM * 128;  // 128 rows x 128 bytes
 constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - 256 /*barriers*/;
 
-template <int BN, int EPI> struct GtCfg {
+// PAIR: two CTAs of a cluster (one TPC) share one 256 x BN tile through tcgen05 cta_group::2 -- each CTA stages its own 128 rows of A
+// and HALF of the B rows, so the shared-memory bytes read per MMA flop drop by a third (a 128 x 192 single-CTA tile needs 106 of the
+// SM's 128 B/clk; the pair needs 75) and each CTA's ring holds more stages.
+template <int BN, int EPI, bool PAIR = false> struct GtCfg {
   static constexpr int A_BYTES = GT_BM * GT_BK * 2;
-  static constexpr int B_BYTES = BN * GT_BK * 2;
+  static constexpr int BNL = PAIR ? BN / 2 : BN;  // B rows staged by this CTA
+  static constexpr int B_BYTES = BNL * GT_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int EPI_BYTES = (EPI == FITB200_EPI_BIAS_GATE_RESID ? 4 : 2) * GT_SLAB_BYTES;  // out x2 (+ resid x2)
   static constexpr int STAGES_RAW = (GT_SMEM_BUDGET - EPI_BYTES) / STAGE_BYTES;
-  static constexpr int STAGES = STAGES_RAW > 6 ? 6 : STAGES_RAW;
+  static constexpr int STAGES = STAGES_RAW > (PAIR ? 8 : 6) ? (PAIR ? 8 : 6) : STAGES_RAW;
   static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;  // 2 accumulator stages, power of two
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
   static_assert(STAGES >= 3, "pipeline too shallow");
+  static_assert(!PAIR || (BNL % 8 == 0 && BN % 16 == 0), "pair tile: N a multiple of 16");
 };
 
 struct GtParams {
@@ -54,12 +59,14 @@ __device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
 // OutT = bf16: a slab is 64 output columns; OutT = float: 32 output columns (both 128 bytes per row).
 // AMN / BMN: the operand is stored contraction-major ([K, M] resp. [K, N] row-major: the dgrad / wgrad GEMMs of the backward pass);
 // its k-slab is fetched as 64-column TMA boxes and read through MN-major SWIZZLE_128B descriptors (tools/probe/umma_probe_mn.cu).
-template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false>
+template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false>
 __global__ void __launch_bounds__(GT_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GtParams p) {
-  using Cfg = GtCfg<BN, EPI>;
+  using Cfg = GtCfg<BN, EPI, PAIR>;
+  static_assert(!PAIR || (!AMN && !BMN), "pair tiles: K-major operands only");
   constexpr int STAGES = Cfg::STAGES;
+  constexpr int TM = PAIR ? 2 * GT_BM : GT_BM;  // rows of one scheduled tile (both CTAs of a pair)
   constexpr bool SWIGLU = EPI == FITB200_EPI_SWIGLU;
   constexpr bool RESID = EPI == FITB200_EPI_BIAS_GATE_RESID;
   constexpr bool ROPE = EPI == FITB200_EPI_BIAS_ROPE;
@@ -85,9 +92,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 6);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tiles_n = ceil_div(p.N, BN), tiles_m = ceil_div(p.M, GT_BM);
+  const int tiles_n = ceil_div(p.N, BN), tiles_m = ceil_div(p.M, TM);
   const int num_tiles = tiles_m * tiles_n;
   const int num_kb = ceil_div(p.K, GT_BK);
+  const uint32_t rank = PAIR ? ptx::cluster_ctarank() : 0u;   // 0 = leader: issues the MMAs of the pair
+  const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;      // scheduling unit (CTA or pair)
+  const int nwork = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int row_off = (int)rank * GT_BM;                                   // this CTA's rows inside the tile
 
   if (threadIdx.x == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -97,17 +108,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], GT_EPI_THREADS);
+      ptx::mbar_init(&tempty_bar[s], (PAIR ? 2 : 1) * GT_EPI_THREADS);
       ptx::mbar_init(&res_bar[s], 1);
     }
     ptx::fence_mbar_init();
   }
-  if (warp == 1) {  // one warp owns TMEM allocation and deallocation
-    ptx::tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
-    ptx::tmem_relinquish();
+  if (warp == 1) {  // one warp (of each CTA) owns TMEM allocation and deallocation
+    if (PAIR) { ptx::tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS); ptx::tmem_relinquish_pair(); }
+    else { ptx::tmem_alloc(tmem_slot, Cfg::TMEM_COLS); ptx::tmem_relinquish(); }
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (PAIR) ptx::cluster_sync();  // the peer's barriers must be initialised before anything is signalled across the pair
+  else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -115,10 +127,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / tiles_n) * GT_BM, n0 = (tile % tiles_n) * BN;
+      for (int tile = wid; tile < num_tiles; tile += nwork) {
+        const int m0 = (tile / tiles_n) * TM + row_off, n0 = (tile % tiles_n) * BN + (int)rank * Cfg::BNL;
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (PAIR) {
+            // both CTAs' bytes are counted on the LEADER's full barrier (the only one the MMA thread waits on)
+            if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+            const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
+            ptx::tma_load_2d_pair(smemA + stage * Cfg::A_BYTES, &tmA, fb, kb * GT_BK, m0);
+            ptx::tma_load_2d_pair(smemB + stage * Cfg::B_BYTES, &tmB, fb, kb * GT_BK, n0);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            continue;
+          }
           ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
           if (AMN) {
 #pragma unroll
@@ -139,13 +160,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::idesc_bf16_f32(GT_BM, BN) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = ptx::idesc_bf16_f32(TM, BN) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = wid; tile < num_tiles; tile += nwork, ++it) {
         const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);  // epilogue has drained this accumulator stage
+        // epilogue (of both CTAs of a pair) has drained this accumulator stage
+        if (PAIR) ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1); else ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -158,12 +180,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int k = 0; k < GT_BK / 16; ++k) {
             // 16 elements along K: K-major = 32 bytes inside the 128-byte swizzle row (+2 in the addr >> 4 field);
             // MN-major = 16 k-rows of 128 bytes (+128)
-            ptx::mma_f16_ss(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0);
+            if (PAIR) ptx::mma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            else ptx::mma_f16_ss(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0);
           }
-          ptx::mma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+          // smem slot reusable once these MMAs retire (pair: the slot of BOTH CTAs)
+          if (PAIR) ptx::mma_commit_pair(&empty_bar[stage], 3); else ptx::mma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        ptx::mma_commit(&tfull_bar[as]);  // accumulator complete
+        if (PAIR) ptx::mma_commit_pair(&tfull_bar[as], 3); else ptx::mma_commit(&tfull_bar[as]);  // accumulator complete
       }
     }
     __syncwarp();
@@ -174,14 +198,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int row = quarter * 32 + lane;     // row inside the tile == TMEM lane
     const bool leader = threadIdx.x == 64;   // first epilogue thread: issues the TMA stores / residual loads
     const uint32_t sw = (uint32_t)(row & 7); // 128B-swizzle phase of this row
-    const int my_tiles = (int)blockIdx.x < num_tiles ? (num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    const int my_tiles = wid < num_tiles ? (num_tiles - 1 - wid) / nwork + 1 : 0;
+    const uint32_t tempty_leader = PAIR ? ptx::mapa(ptx::smem_u32(&tempty_bar[0]), 0) : 0u;  // the leader's tempty_bar[0]
     const int total_slabs = my_tiles * NSLAB;
 
     // residual slab q (running index over this CTA's tiles) -> TMA load into resid buffer q & 1
     auto issue_resid = [&](int qq) {
       if (qq >= total_slabs) return;
-      const int tile = blockIdx.x + (qq / NSLAB) * gridDim.x, slab = qq % NSLAB;
-      const int rm0 = (tile / tiles_n) * GT_BM, rn0 = (tile % tiles_n) * BN + slab * OUTC;
+      const int tile = wid + (qq / NSLAB) * nwork, slab = qq % NSLAB;
+      const int rm0 = (tile / tiles_n) * TM + row_off, rn0 = (tile % tiles_n) * BN + slab * OUTC;
       ptx::mbar_arrive_expect_tx(&res_bar[qq & 1], GT_SLAB_BYTES);
       ptx::tma_load_2d(smemRes + (qq & 1) * GT_SLAB_BYTES, &tmRes, &res_bar[qq & 1], rn0, rm0);
     };
@@ -189,9 +214,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     int q = 0;  // running slab index
     for (int it = 0; it < my_tiles; ++it) {
-      const int tile = blockIdx.x + it * gridDim.x;
+      const int tile = wid + it * nwork;
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-      const int m0 = (tile / tiles_n) * GT_BM, n0 = (tile % tiles_n) * BN;
+      const int m0 = (tile / tiles_n) * TM + row_off, n0 = (tile % tiles_n) * BN;
       const int m = min(m0 + row, p.M - 1);
       const float* gate_row = nullptr;
       if (RESID) gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
@@ -305,7 +330,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (slab == NSLAB - 1) {  // accumulator fully read: hand the TMEM stage back to the MMA warp
           ptx::tc_fence_before();
-          ptx::mbar_arrive(&tempty_bar[as]);
+          if (PAIR) ptx::mbar_arrive_cluster(tempty_leader + as * 8); else ptx::mbar_arrive(&tempty_bar[as]);
         }
         ptx::fence_proxy_async_smem();  // make the st.shared visible to the TMA (async proxy)
         ptx::named_bar_sync(1, GT_EPI_THREADS);
@@ -320,10 +345,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if (PAIR) ptx::cluster_sync();  // neither CTA may retire (or free TMEM) while the pair's MMAs / barrier traffic are in flight
+  else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if (PAIR) ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS); else ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
@@ -362,13 +388,13 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int dtype, long rows, long
   return FITB200_OK;
 }
 
-template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false>
+template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false>
 static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
-  using Cfg = GtCfg<BN, EPI>;
+  using Cfg = GtCfg<BN, EPI, PAIR>;
   CUtensorMap tmA, tmB, tmOut, tmRes;
   int rc = AMN ? make_tmap(&tmA, a.A, FITB200_BF16, a.K, a.M, a.lda, GT_BK, 64) : make_tmap(&tmA, a.A, FITB200_BF16, a.M, a.K, a.lda, GT_BM, GT_BK);
   if (rc) return rc;
-  rc = BMN ? make_tmap(&tmB, a.B, FITB200_BF16, a.K, a.N, a.ldb, GT_BK, 64) : make_tmap(&tmB, a.B, FITB200_BF16, a.N, a.K, a.ldb, BN, GT_BK);
+  rc = BMN ? make_tmap(&tmB, a.B, FITB200_BF16, a.K, a.N, a.ldb, GT_BK, 64) : make_tmap(&tmB, a.B, FITB200_BF16, a.N, a.K, a.ldb, Cfg::BNL, GT_BK);
   if (rc) return rc;
   const int outc = 128 / (int)sizeof(OutT);
   const long n_out = EPI == FITB200_EPI_SWIGLU ? a.N / 2 : a.N;
@@ -383,12 +409,25 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   p.M = a.M; p.N = a.N; p.K = a.K; p.bias = a.bias;
   p.gate = a.gate; p.ld_gate = a.ld_gate; p.rows_per_sample = a.rows_per_sample;
   p.rope_freqs = a.rope_freqs; p.rope_rows = a.rope_rows; p.rope_tokens = a.rope_tokens; p.rope_hd = a.rope_head_dim; p.rope_cols = a.rope_cols;
-  auto kern = gemm_tc_kernel<BN, EPI, OutT, AMN, BMN>;
+  auto kern = gemm_tc_kernel<BN, EPI, OutT, AMN, BMN, PAIR>;
   static bool attr_done = false;  // per template instantiation
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) { set_last_error("gemm_bf16_tc: cannot set %d bytes of dynamic smem: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
     attr_done = true;
+  }
+  if (PAIR) {
+    const int tiles = ceil_div(a.M, 2 * GT_BM) * ceil_div(a.N, BN);
+    const int pairs = tiles < sm_count() / 2 ? tiles : sm_count() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(GT_THREADS); cfg.dynamicSmemBytes = Cfg::SMEM_BYTES; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmOut, tmRes, p);
+    if (e != cudaSuccess) { set_last_error("gemm_bf16_tc: pair launch failed: %s", cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
+    return FITB200_OK;
   }
   const int tiles = ceil_div(a.M, GT_BM) * ceil_div(a.N, BN);
   const int grid = tiles < sm_count() ? tiles : sm_count();
@@ -404,6 +443,19 @@ static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
     if (a.a_mn && a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, true>(a, s);
     if (a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, true>(a, s);
     return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, false>(a, s);
+  }
+  // K-major operands: CTA pairs (256 x BN tiles, cta_group::2) whenever there are at least two row blocks; FITB200_GEMM_PAIR=0 forces single-CTA tiles
+  static const bool pair_ok = [] { const char* e = getenv("FITB200_GEMM_PAIR"); return !(e && e[0] == '0'); }();
+  if (pair_ok && a.M > GT_BM) {
+    switch (a.epilogue) {
+      case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, false, true>(a, s);
+      case FITB200_EPI_BIAS_SILU: return launch_tc<BN, FITB200_EPI_BIAS_SILU, OutT, false, false, true>(a, s);
+      case FITB200_EPI_BIAS_ROPE: break;  // measured on B200: the RoPE epilogue is the critical path and the pair couples two of them (1.29 vs 1.03 ms)
+      case FITB200_EPI_SWIGLU:
+        if constexpr (BN != 192) return launch_tc<BN, FITB200_EPI_SWIGLU, OutT, false, false, true>(a, s);
+        break;
+      case FITB200_EPI_BIAS_GATE_RESID: return launch_tc<BN, FITB200_EPI_BIAS_GATE_RESID, OutT, false, false, true>(a, s);
+    }
   }
   switch (a.epilogue) {
     case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT>(a, s);
