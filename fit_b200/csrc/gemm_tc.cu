@@ -23,6 +23,7 @@ constexpr int GT_BM = 128, GT_BK = 64;
 constexpr int GT_THREADS = 320;  // producer + mma + 8 epilogue warps
 constexpr int GT_EPI_THREADS = 256;  // two warps per TMEM lane quarter: each takes half of a slab's columns
 constexpr int GT_SLAB_BYTES = GT_BM * 128;  // 128 rows x 128 bytes
+constexpr int GT_ROPE_MAX_HD = 72;          // head dims up to this keep the tile's RoPE rows in shared memory (FiT: 64, 72)
 constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - 256 /*barriers*/;
 
 // PAIR: two CTAs of a cluster (one TPC) share one 256 x BN tile through tcgen05 cta_group::2 -- each CTA stages its own 128 rows of A
@@ -33,7 +34,9 @@ template <int BN, int EPI, bool PAIR = false> struct GtCfg {
   static constexpr int BNL = PAIR ? BN / 2 : BN;  // B rows staged by this CTA
   static constexpr int B_BYTES = BNL * GT_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int EPI_BYTES = (EPI == FITB200_EPI_BIAS_GATE_RESID ? 4 : 2) * GT_SLAB_BYTES;  // out x2 (+ resid x2)
+  // out x2 (+ resid x2) (+ the RoPE table rows of the tile's 128 tokens, fp32, row stride head_dim + 4 words: conflict-free float4 reads)
+  static constexpr int ROPE_BYTES = EPI == FITB200_EPI_BIAS_ROPE ? GT_BM * (GT_ROPE_MAX_HD + 4) * 4 : 0;
+  static constexpr int EPI_BYTES = (EPI == FITB200_EPI_BIAS_GATE_RESID ? 4 : 2) * GT_SLAB_BYTES + ROPE_BYTES;
   static constexpr int STAGES_RAW = (GT_SMEM_BUDGET - EPI_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > (PAIR ? 8 : 6) ? (PAIR ? 8 : 6) : STAGES_RAW;
   static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;  // 2 accumulator stages, power of two
@@ -47,6 +50,7 @@ struct GtParams {
   const float* bias;
   const float* gate; long ld_gate; int rows_per_sample;
   const float* rope_freqs; int rope_rows, rope_tokens, rope_hd, rope_cols;
+  int dbg;  // FITB200_GEMM_DBG=1: epilogue releases the accumulator without reading it (mainloop ceiling measurement only)
 };
 
 __device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
@@ -67,6 +71,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   static_assert(!PAIR || (!AMN && !BMN), "pair tiles: K-major operands only");
   constexpr int STAGES = Cfg::STAGES;
   constexpr int TM = PAIR ? 2 * GT_BM : GT_BM;  // rows of one scheduled tile (both CTAs of a pair)
+  constexpr int NGRAN = PAIR ? 32 : 16;         // granularity of the last column tile's MMA N
   constexpr bool SWIGLU = EPI == FITB200_EPI_SWIGLU;
   constexpr bool RESID = EPI == FITB200_EPI_BIAS_GATE_RESID;
   constexpr bool ROPE = EPI == FITB200_EPI_BIAS_ROPE;
@@ -83,6 +88,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* smemB = smem + STAGES * Cfg::A_BYTES;
   uint8_t* smemOut = smem + STAGES * Cfg::STAGE_BYTES;          // [2][128 rows][128 B]
   uint8_t* smemRes = smemOut + 2 * GT_SLAB_BYTES;               // [2][128 rows][128 B]  (RESID only)
+  float* smemRope = reinterpret_cast<float*>(smemOut + 2 * GT_SLAB_BYTES);  // [128 rows][head_dim + 4]  (ROPE only)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
   uint64_t* full_bar = bars;                     // [STAGES]  TMA -> MMA
   uint64_t* empty_bar = bars + STAGES;           // [STAGES]  MMA -> TMA
@@ -128,7 +134,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = wid; tile < num_tiles; tile += nwork) {
-        const int m0 = (tile / tiles_n) * TM + row_off, n0 = (tile % tiles_n) * BN + (int)rank * Cfg::BNL;
+        // the last column tile may be narrower (MMA N = nn): in a pair the second CTA's half of B then starts nn / 2 rows in
+        const int n0t = (tile % tiles_n) * BN, nn = min(BN, (p.N - n0t + NGRAN - 1) / NGRAN * NGRAN);
+        const int m0 = (tile / tiles_n) * TM + row_off, n0 = n0t + (int)rank * (nn / 2);
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           if (PAIR) {
@@ -161,7 +169,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0 && rank == 0) {
-      constexpr uint32_t idesc = ptx::idesc_bf16_f32(TM, BN) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
+      constexpr uint32_t idesc0 = ptx::idesc_bf16_f32(TM, 0) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int tile = wid; tile < num_tiles; tile += nwork, ++it) {
@@ -170,6 +178,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (PAIR) ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1); else ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
+        // N = 192 issues at the rate of N = 256 on B200 (measured): tiles are 256 (or 128) wide and only the last one is cut to what is left
+        const int nn = min(BN, (p.N - (tile % tiles_n) * BN + NGRAN - 1) / NGRAN * NGRAN);
+        const uint32_t idesc = idesc0 | ((uint32_t)(nn >> 3) << 17);
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
@@ -213,6 +224,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (RESID && leader) { issue_resid(0); issue_resid(1); }
 
     int q = 0;  // running slab index
+    int rope_m0 = -1;  // row block whose RoPE rows are in smemRope
     for (int it = 0; it < my_tiles; ++it) {
       const int tile = wid + it * nwork;
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
@@ -222,12 +234,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (RESID) gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
       const float* rope_row = nullptr;  // (cos, sin) pairs of this row's token
       if (ROPE) {
-        const int smp = m / p.rope_tokens, tok = m - smp * p.rope_tokens;
-        rope_row = p.rope_freqs + ((size_t)(p.rope_rows == 1 ? 0 : smp) * p.rope_tokens + tok) * p.rope_hd;
+        if (p.rope_hd <= GT_ROPE_MAX_HD) {
+          // the table rows of this tile's 128 tokens are staged in shared memory once per row block (column tiles of one row
+          // block are consecutive): per-thread global reads of 288-byte-strided rows were the epilogue's critical path
+          const int rs = p.rope_hd + 4;
+          if (m0 != rope_m0) {
+            const int q4 = p.rope_hd >> 2, total = GT_BM * q4, et = threadIdx.x - 64;
+            for (int i = et; i < total; i += GT_EPI_THREADS) {
+              const int rr = i / q4, c4 = i - rr * q4;
+              const int mm = min(m0 + rr, p.M - 1), smp = mm / p.rope_tokens, tok = mm - smp * p.rope_tokens;
+              const float4 v = __ldg(reinterpret_cast<const float4*>(p.rope_freqs + ((size_t)(p.rope_rows == 1 ? 0 : smp) * p.rope_tokens + tok) * p.rope_hd) + c4);
+              *reinterpret_cast<float4*>(smemRope + rr * rs + c4 * 4) = v;
+            }
+            rope_m0 = m0;  // visible to every epilogue thread after the first slab's named barrier
+          }
+          rope_row = smemRope + row * rs;
+        } else {
+          const int smp = m / p.rope_tokens, tok = m - smp * p.rope_tokens;
+          rope_row = p.rope_freqs + ((size_t)(p.rope_rows == 1 ? 0 : smp) * p.rope_tokens + tok) * p.rope_hd;
+        }
       }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+      if (p.dbg) {
+        ptx::tc_fence_before();
+        if (PAIR) ptx::mbar_arrive_cluster(tempty_leader + as * 8); else ptx::mbar_arrive(&tempty_bar[as]);
+        q += NSLAB;
+        continue;
+      }
 #pragma unroll 1
       for (int slab = 0; slab < NSLAB; ++slab, ++q) {
         const int buf = q & 1;
@@ -252,7 +287,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const bool rot = nacc + (half * 4 + jj) * CW < p.rope_cols;
 #pragma unroll
               for (int i4 = 0; i4 < CW / 4; ++i4)
-                fq[ROPE ? jj : 0][i4] = rot ? __ldg(reinterpret_cast<const float4*>(rope_row + hcol + i4 * 4)) : make_float4(1.f, 0.f, 1.f, 0.f);
+                fq[ROPE ? jj : 0][i4] = rot ? *reinterpret_cast<const float4*>(rope_row + hcol + i4 * 4) : make_float4(1.f, 0.f, 1.f, 0.f);
               hcol += CW;
               if (hcol >= p.rope_hd) hcol -= p.rope_hd;
             }
@@ -409,6 +444,8 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   p.M = a.M; p.N = a.N; p.K = a.K; p.bias = a.bias;
   p.gate = a.gate; p.ld_gate = a.ld_gate; p.rows_per_sample = a.rows_per_sample;
   p.rope_freqs = a.rope_freqs; p.rope_rows = a.rope_rows; p.rope_tokens = a.rope_tokens; p.rope_hd = a.rope_head_dim; p.rope_cols = a.rope_cols;
+  static const int dbg = [] { const char* e = getenv("FITB200_GEMM_DBG"); return e ? atoi(e) : 0; }();
+  p.dbg = dbg;
   auto kern = gemm_tc_kernel<BN, EPI, OutT, AMN, BMN, PAIR>;
   static bool attr_done = false;  // per template instantiation
   if (!attr_done) {
@@ -450,7 +487,7 @@ static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
     switch (a.epilogue) {
       case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, false, true>(a, s);
       case FITB200_EPI_BIAS_SILU: return launch_tc<BN, FITB200_EPI_BIAS_SILU, OutT, false, false, true>(a, s);
-      case FITB200_EPI_BIAS_ROPE: break;  // measured on B200: the RoPE epilogue is the critical path and the pair couples two of them (1.29 vs 1.03 ms)
+      case FITB200_EPI_BIAS_ROPE: return launch_tc<BN, FITB200_EPI_BIAS_ROPE, OutT, false, false, true>(a, s);
       case FITB200_EPI_SWIGLU:
         if constexpr (BN != 192) return launch_tc<BN, FITB200_EPI_SWIGLU, OutT, false, false, true>(a, s);
         break;
@@ -472,14 +509,10 @@ static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
 
 template <typename OutT>
 static int dispatch_bn(const fitb200_gemm_args& a, cudaStream_t s) {
-  // widest tile with the least padded columns (3456, 1152 -> 192; 6144, 2304, 768 -> 256)
-  int best = 256; long best_waste = (long)ceil_div(a.N, 256) * 256 - a.N;
-  const int cand[2] = {192, 128};
-  for (int c : cand) {
-    if (c == 192 && a.epilogue == FITB200_EPI_SWIGLU) continue;
-    long w = (long)ceil_div(a.N, c) * c - a.N;
-    if (w < best_waste) { best = c; best_waste = w; }
-  }
+  // 256-wide tiles (the last one of a row is cut to the columns that are left); N = 192 MMAs cost as much as N = 256 ones.
+  // FITB200_GEMM_BN=128|192|256 overrides (tuning / tests)
+  static const int force = [] { const char* e = getenv("FITB200_GEMM_BN"); return e ? atoi(e) : 0; }();
+  const int best = force ? force : (a.N <= 128 ? 128 : 256);
   if (best == 256) return dispatch_epi<256, OutT>(a, s);
   if (best == 192) return dispatch_epi<192, OutT>(a, s);
   return dispatch_epi<128, OutT>(a, s);
