@@ -132,75 +132,134 @@ __global__ void cond_combine_kernel(const float* __restrict__ t_emb, int t_rows,
 }
 
 // --------------------------------------------------------------------------------------------
-// LayerNorm + modulate.  One CTA = LN_ROWS consecutive rows of ONE sample: (1 + scale) and shift of that sample are
-// staged once in shared memory (they are 4x the bytes of a bf16 row, so re-reading them per row from L2 made the first
-// version L2-bound at 29 % of HBM peak); one warp per row, row cached in registers (D <= 2048, D % 8 == 0), 16-byte accesses.
+// LayerNorm + modulate.  One CTA = 8 warps x RPW consecutive rows of ONE sample: (1 + scale) and shift of that sample are staged
+// once in shared memory in a lane-major float4 layout (no bank conflicts) and read ONCE per RPW rows; a warp keeps its RPW = 2
+// bf16 rows packed in registers (loads of all four in flight together), D <= 2048, D % 8 == 0, 16-byte accesses.
+// History on B200 (R=512 XL/2): one row per warp + [D] smem table = 0.158 ms (l1tex 74 %, 10.6 M bank conflicts per launch).
 // --------------------------------------------------------------------------------------------
 constexpr int LN_MAXV = 8;    // 8 vectors of 8 per lane
-constexpr int LN_ROWS = 32;   // rows per CTA (8 warps x 4 rows)
+constexpr int LN_ITERS = 4;   // row rounds per CTA: the staged modulation is reused by 8 warps x RPW x LN_ITERS rows
+
+// raw 8-element row fragments: bf16 rows stay packed (4 registers) so that one warp can hold several rows in flight
+template <typename T> struct Raw8;
+template <> struct Raw8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) { a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 4); }
+  __device__ __forceinline__ void get(float (&f)[8]) const { f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w; }
+};
+template <> struct Raw8<__nv_bfloat16> {
+  uint4 a;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { a = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void get(float (&f)[8]) const {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&a);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float2 t = __bfloat1622float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+  }
+};
+template <typename InT> struct LnRows { static constexpr int RPW = sizeof(InT) == 2 ? 2 : 1; };  // rows one warp holds in flight
 
 template <typename InT, typename OutT, int NV>
-__global__ void __launch_bounds__(256) ln_modulate_kernel(const InT* __restrict__ x, int M, int D, int rows_per_sample,
+__global__ void __launch_bounds__(256, 2) ln_modulate_kernel(const InT* __restrict__ x, int M, int D, int rows_per_sample,
                                                           int blocks_per_sample, const float* __restrict__ shift,
                                                           const float* __restrict__ scale, long ld_mod, OutT* __restrict__ out,
                                                           float* __restrict__ mean_out, float* __restrict__ rstd_out) {
-  extern __shared__ __align__(16) float ln_mod[];  // [D] 1+scale | [D] shift
+  constexpr int RPW = LnRows<InT>::RPW;
+  // 1+scale and shift of this CTA's sample as float4 [i][half][lane]: lane l's two float4 of vector (l + 32 i) -- conflict-free reads
+  extern __shared__ __align__(16) float4 ln_mod4[];
+  float4* sc4 = ln_mod4;
+  float4* sh4 = ln_mod4 + NV * 64;
   const int sample = blockIdx.x / blocks_per_sample, blk = blockIdx.x - sample * blocks_per_sample;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nvec = D >> 3;
   const size_t mrow = (size_t)sample * ld_mod;
+  for (int it = 0; it < LN_ITERS; ++it) {
+  const int rl0 = ((blk * LN_ITERS + it) * 8 + warp) * RPW;  // first row (inside the sample) of this warp in this round
+  if (it > 0 && rl0 >= rows_per_sample) break;  // (round 0 always reaches the __syncthreads below)
+  Raw8<InT> v[RPW][NV];
+  bool live[RPW];
+#pragma unroll
+  for (int j = 0; j < RPW; ++j) {
+    const int row = sample * rows_per_sample + rl0 + j;
+    live[j] = rl0 + j < rows_per_sample && row < M;
+    if (live[j]) {
+      const InT* xr = x + (size_t)row * D;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vi = lane + i * 32;
+        if (vi < nvec) v[j][i].load(xr + vi * 8);
+      }
+    }
+  }
+  // modulation staging after the first row loads are in flight (independent latencies overlap)
+  if (it == 0) {
   for (int i = threadIdx.x; i < D / 4; i += blockDim.x) {
     float4 sc = *reinterpret_cast<const float4*>(scale + mrow + i * 4);
     const float4 sh = *reinterpret_cast<const float4*>(shift + mrow + i * 4);
     sc.x += 1.0f; sc.y += 1.0f; sc.z += 1.0f; sc.w += 1.0f;
-    *reinterpret_cast<float4*>(ln_mod + i * 4) = sc;
-    *reinterpret_cast<float4*>(ln_mod + D + i * 4) = sh;
+    const int vi = i >> 1, pos = ((vi >> 5) * 2 + (i & 1)) * 32 + (vi & 31);
+    sc4[pos] = sc;
+    sh4[pos] = sh;
   }
   __syncthreads();
-  const int r_end = min(rows_per_sample, (blk + 1) * LN_ROWS);
-  for (int rl = blk * LN_ROWS + warp; rl < r_end; rl += 8) {
-    const int row = sample * rows_per_sample + rl;
-    if (row >= M) break;
-    const InT* xr = x + (size_t)row * D;
-    Vec8<InT> v[NV];
+  }
+  float mu[RPW], rstd[RPW];
+#pragma unroll
+  for (int j = 0; j < RPW; ++j) {
     float s = 0.f;
+    if (live[j]) {
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      int vi = lane + i * 32;
-      if (vi < nvec) {
-        v[i] = Vec8<InT>::load(xr + vi * 8);
+      for (int i = 0; i < NV; ++i) {
+        if (lane + i * 32 < nvec) {
+          float f[8];
+          v[j][i].get(f);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) s += v[i].v[e];
+          for (int e = 0; e < 8; ++e) s += f[e];
+        }
       }
     }
-    const float mu = warp_sum(s) / (float)D;
+    mu[j] = warp_sum(s) / (float)D;
+  }
+#pragma unroll
+  for (int j = 0; j < RPW; ++j) {
     float q = 0.f;
+    if (live[j]) {
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      int vi = lane + i * 32;
-      if (vi < nvec) {
+      for (int i = 0; i < NV; ++i) {
+        if (lane + i * 32 < nvec) {
+          float f[8];
+          v[j][i].get(f);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { float d = v[i].v[e] - mu; q = fmaf(d, d, q); }
+          for (int e = 0; e < 8; ++e) { const float d = f[e] - mu[j]; q = fmaf(d, d, q); }
+        }
       }
     }
-    const float rstd = rsqrtf(warp_sum(q) / (float)D + 1e-6f);
-    if (lane == 0) {
-      if (mean_out) mean_out[row] = mu;
-      if (rstd_out) rstd_out[row] = rstd;
+    rstd[j] = rsqrtf(warp_sum(q) / (float)D + 1e-6f);
+    if (live[j] && lane == 0) {
+      const int row = sample * rows_per_sample + rl0 + j;
+      if (mean_out) mean_out[row] = mu[j];
+      if (rstd_out) rstd_out[row] = rstd[j];
     }
-    OutT* orow = out + (size_t)row * D;
+  }
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      int vi = lane + i * 32;
-      if (vi < nvec) {
-        Vec8<float> sc = Vec8<float>::load(ln_mod + vi * 8);
-        Vec8<float> sh = Vec8<float>::load(ln_mod + D + vi * 8);
-        Vec8<OutT> o;
+  for (int i = 0; i < NV; ++i) {
+    if (lane + i * 32 < nvec) {
+      const float4 c0 = sc4[(i * 2) * 32 + lane], c1 = sc4[(i * 2 + 1) * 32 + lane];
+      const float4 h0 = sh4[(i * 2) * 32 + lane], h1 = sh4[(i * 2 + 1) * 32 + lane];
+      const float sc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+      const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o.v[e] = fmaf((v[i].v[e] - mu) * rstd, sc.v[e], sh.v[e]);
-        o.store(orow + vi * 8);
+      for (int j = 0; j < RPW; ++j) {
+        if (live[j]) {
+          float f[8];
+          v[j][i].get(f);
+          Vec8<OutT> o;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o.v[e] = fmaf((f[e] - mu[j]) * rstd[j], sc[e], sh[e]);
+          o.store(out + (size_t)(sample * rows_per_sample + rl0 + j) * D + (lane + i * 32) * 8);
+        }
       }
     }
+  }
   }
 }
 
@@ -445,10 +504,10 @@ __global__ void add_i64_kernel(int64_t* __restrict__ idx, int n, int64_t delta) 
 template <typename InT, typename OutT>
 static void launch_ln(const void* x, int M, int D, int rows_per_sample, const float* shift, const float* scale, int64_t ld_mod,
                       void* out, float* mean, float* rstd, cudaStream_t s) {
-  const int samples = ceil_div(M, rows_per_sample), bps = ceil_div(rows_per_sample, LN_ROWS);
+  const int samples = ceil_div(M, rows_per_sample), bps = ceil_div(rows_per_sample, 8 * LnRows<InT>::RPW * LN_ITERS);
   const dim3 grid((unsigned)(samples * bps));
-  const size_t smem = (size_t)2 * D * sizeof(float);
   const int nv = ceil_div(D >> 3, 32);
+  const size_t smem = (size_t)nv * 128 * sizeof(float4);
 #define FITB200_LN_CASE(NV)                                                                                              \
   case NV:                                                                                                               \
     ln_modulate_kernel<InT, OutT, NV><<<grid, 256, smem, s>>>((const InT*)x, M, D, rows_per_sample, bps, shift, scale, ld_mod, \
