@@ -20,6 +20,7 @@
 // Keys are held as two 128-row halves: [half][chunk][128 rows][16 B].
 // The operand conventions used here (no-swizzle LBO/SBO roles, MN-major B, A-from-TMEM packing, accumulator at an
 // unaligned column) are pinned by tools/probe/umma_probe.cu.
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -356,11 +357,16 @@ static int launch_attn_tc(const void* qkv, const float* freqs, int freqs_rows, c
   return FITB200_OK;
 }
 
+int attn_fwd_tc2(const void* qkv, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s);
+
 // bf16, T <= 256: the tcgen05 kernel.  Called from fitb200_attn_fwd (attn_mma.cu).  prerotated: q, k already carry the RoPE.
 int attn_fwd_tc(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d,
                 int prerotated, void* out, float* lse, cudaStream_t s) {
   if (prerotated) {
     if (((uintptr_t)qkv & 15) != 0) { set_last_error("attn_fwd: qkv must be 16-byte aligned"); return FITB200_ERR_INVALID_ARG; }
+    // persistent warp-specialised schedule (attn_tc2.cu); FITB200_ATTN_V1=1 keeps the one-tile-per-CTA kernel below
+    static const bool v1 = [] { const char* e = getenv("FITB200_ATTN_V1"); return e && e[0] == '1'; }();
+    if (!v1 && (d == 64 || d == 72) && ((uintptr_t)out & 15) == 0) return attn_fwd_tc2(qkv, kv_len, mask, R, Tn, h, d, out, lse, s);
     if (d == 64) return launch_attn_tc<64, true>(qkv, freqs, freqs_rows, kv_len, mask, R, Tn, h, out, lse, s);
     if (d == 72) return launch_attn_tc<72, true>(qkv, freqs, freqs_rows, kv_len, mask, R, Tn, h, out, lse, s);
   } else {
