@@ -138,9 +138,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       int uq = 0, ic = 0;
       bool have_prev = false;
       int p_g = 0, p_slot = 0, p_nk16 = 0, p_u = 0; uint32_t p_ph = 0; bool p_last = false;
+      auto pv_ready = [&]() { return ptx::mbar_try_wait(&p_ready[p_g], (p_u >> 1) & 1) && ptx::mbar_try_wait(&v_full[p_slot], p_ph); };
       auto issue_pv = [&]() {
-        ptx::mbar_wait(&p_ready[p_g], (p_u >> 1) & 1);
-        ptx::mbar_wait(&v_full[p_slot], p_ph);
         ptx::tc_fence_after();
         const uint32_t tr = tb + p_g * 256;
         const uint32_t idesc = ptx::idesc_bf16_f32(A2_BQ, DP) | (1u << 16);  // B (= V) is MN-major
@@ -163,9 +162,17 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const int slot = ic & 1; const uint32_t ph = (ic >> 1) & 1;
         for (int qt = 0; qt < nlive; ++qt, ++uq) {
           const int g = uq & 1, qb = uq % A2_NQ;
-          ptx::mbar_wait(&t_empty[g], ((uq >> 1) & 1) ^ 1);  // the group has drained O of unit uq - 2
-          ptx::mbar_wait(&q_full[qb], (uq / A2_NQ) & 1);
-          ptx::mbar_wait(&k_full[slot], ph);
+          // event driven: P V of the previous unit (other group) goes out as soon as its softmax is done, even while S of this
+          // unit still waits for ITS group to drain O of unit uq - 2 -- issuing strictly in order locked the two groups in step
+          bool pv_done = !have_prev;
+          uint32_t spins = 0;
+          for (;;) {
+            if (!pv_done && pv_ready()) { issue_pv(); pv_done = true; }
+            if (ptx::mbar_try_wait(&t_empty[g], ((uq >> 1) & 1) ^ 1) && ptx::mbar_try_wait(&q_full[qb], (uq / A2_NQ) & 1) &&
+                ptx::mbar_try_wait(&k_full[slot], ph))
+              break;
+            if (++spins > (1u << 24)) __trap();
+          }
           ptx::tc_fence_after();
           const uint32_t tr = tb + g * 256;
 #pragma unroll
@@ -182,12 +189,12 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             }
           }
           ptx::mma_commit(&s_full[g]);
-          if (have_prev) issue_pv();
+          if (!pv_done) { while (!pv_ready()) { if (++spins > (1u << 24)) __trap(); } issue_pv(); }
           have_prev = true; p_g = g; p_slot = slot; p_nk16 = nk16; p_u = uq; p_ph = ph; p_last = qt == nlive - 1;
         }
         ++ic;
       }
-      if (have_prev) issue_pv();
+      if (have_prev) { uint32_t spins = 0; while (!pv_ready()) { if (++spins > (1u << 24)) __trap(); } issue_pv(); }
     }
     __syncwarp();
   } else {
@@ -203,7 +210,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const uint32_t lane_base = tb + g * 256 + ((uint32_t)(quarter * 32) << 16);
     const float sl2 = rsqrtf((float)HD) * 1.4426950408889634f;  // softmax scale folded with log2(e)
     const int bar_id = 1 + g;
-    int uq = 0;
+    int uq = 0, pend_qb = -1;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
       const int r = item / h, head = item - r * h;
       const int kvl = min(kv_len[r], Tn);
@@ -224,6 +231,11 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         if ((uq & 1) != g) continue;
         const int q0 = qt * A2_BQ, qb = uq % A2_NQ;
         const uint32_t uph = (uq >> 1) & 1;
+        if (gt == 0 && pend_qb >= 0) {
+          ptx::tma_store_wait_read<0>();
+          ptx::mbar_arrive(&q_empty[pend_qb]);  // the producer may refill that Q buffer
+          pend_qb = -1;
+        }
         {
           const int key = gw * 32 + lane;
           const bool v = key < nk && (mask == nullptr || mask[(size_t)r * Tn + key] != 0);
@@ -330,8 +342,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         if (gt == 0) {
           a2_tma_store_3d(&tmOut, sQ + qb * BLOCK, head * HD, q0, r);
           ptx::tma_store_commit();
-          ptx::tma_store_wait_read<0>();
-          ptx::mbar_arrive(&q_empty[qb]);  // the producer may refill this Q buffer
+          pend_qb = qb;  // released at the start of this group's next unit (the store needs time to read the staging)
         }
       }
     }
