@@ -512,14 +512,9 @@ static int dispatch_bn(const fitb200_gemm_args& a, cudaStream_t s) {
   // 256-wide tiles (the last one of a row is cut to the columns that are left); N = 192 MMAs cost as much as N = 256 ones.
   // FITB200_GEMM_BN=128|192|256 overrides (tuning / tests)
   static const int force = [] { const char* e = getenv("FITB200_GEMM_BN"); return e ? atoi(e) : 0; }();
-  // small problems (training: M = 8192 rows) are dominated by wave quantisation: pick the width with the fewer wave x tile-cost units
-  auto cost = [&](int bn) {
-    const bool pair = !a.a_mn && !a.b_mn && a.M > GT_BM;
-    const long tm = ceil_div((long)a.M, (long)(pair ? 2 * GT_BM : GT_BM)), units = pair ? sm_count() / 2 : sm_count();
-    const long waves = ceil_div(tm * ceil_div((long)a.N, (long)bn), units);
-    return waves * bn;
-  };
-  const int best = force ? force : (a.N <= 128 || cost(128) < cost(256) ? 128 : 256);
+  // (tried: 128-wide tiles when they need fewer wave x width units at training sizes -- 47.4 vs 42.5 ms per XL/2 step: N = 128 tiles are
+  // shared-memory-bandwidth bound, so 256 stays)
+  const int best = force ? force : (a.N <= 128 ? 128 : 256);
   if (best == 256) return dispatch_epi<256, OutT>(a, s);
   if (best == 192) return dispatch_epi<192, OutT>(a, s);
   return dispatch_epi<128, OutT>(a, s);
