@@ -114,7 +114,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], (PAIR ? 2 : 1) * GT_EPI_THREADS);
+      ptx::mbar_init(&tempty_bar[s], PAIR ? 2 * (GT_EPI_THREADS / 32) : GT_EPI_THREADS);  // pair: one arrival per epilogue warp of both CTAs
       ptx::mbar_init(&res_bar[s], 1);
     }
     ptx::fence_mbar_init();
@@ -259,7 +259,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
       if (p.dbg) {
         ptx::tc_fence_before();
-        if (PAIR) ptx::mbar_arrive_cluster(tempty_leader + as * 8); else ptx::mbar_arrive(&tempty_bar[as]);
+        if (PAIR) { __syncwarp(); if (lane == 0) ptx::mbar_arrive_cluster_relaxed(tempty_leader + as * 8); } else ptx::mbar_arrive(&tempty_bar[as]);
         q += NSLAB;
         continue;
       }
@@ -365,7 +365,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (slab == NSLAB - 1) {  // accumulator fully read: hand the TMEM stage back to the MMA warp
           ptx::tc_fence_before();
-          if (PAIR) ptx::mbar_arrive_cluster(tempty_leader + as * 8); else ptx::mbar_arrive(&tempty_bar[as]);
+          if (PAIR) {
+            // one relaxed arrival per warp: a release.cluster arrive by every thread cost a MEMBAR + ERRBAR each (9 % of the epilogue samples)
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_cluster_relaxed(tempty_leader + as * 8);
+          } else {
+            ptx::mbar_arrive(&tempty_bar[as]);
+          }
         }
         ptx::fence_proxy_async_smem();  // make the st.shared visible to the TMA (async proxy)
         ptx::named_bar_sync(1, GT_EPI_THREADS);

@@ -127,6 +127,11 @@ __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
 }
+// same without the cluster-scope release (which costs a MEMBAR + ERRBAR): for hand-offs that order no memory, e.g. "TMEM accumulator
+// drained" after tcgen05.wait::ld + tcgen05.fence::before_thread_sync
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
+}
 // wait with cluster-scope acquire: the arrivals come from both CTAs of the pair
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0, ok = 0;

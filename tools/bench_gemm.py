@@ -27,6 +27,21 @@ cases = {
     "proj+gate": (lambda: ops.gemm(att, w_proj, b_proj, xs, EPI_BIAS_GATE_RESID, gate=gate, ld_gate=D, rows_per_sample=T, resid=xs), 2.0 * M * D * D),
 }
 scratch = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device=dev)
+# box normaliser: cuBLAS bf16 GEMMs of the same shapes (no epilogue), back to back
+cub = {}
+for nm, (A, Wt) in {"swiglu": (h, w_fc1), "qkv": (h, w_qkv), "fc2+gate": (gg, w_fc2), "proj+gate": (att, w_proj)}.items():
+    o = torch.empty(A.shape[0], Wt.shape[0], dtype=bf, device=dev)
+    for _ in range(3):
+        torch.matmul(A, Wt.t(), out=o)
+    torch.cuda.synchronize()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for _ in range(30):
+        torch.matmul(A, Wt.t(), out=o)
+    c1.record(); torch.cuda.synchronize()
+    cub[nm] = c0.elapsed_time(c1) / 30
+    del o
+cub["qkv+rope"] = cub["qkv"]
 print("pair =", os.environ.get("FITB200_GEMM_PAIR", "1"))
 for name, (fn, fl) in cases.items():
     fn(); fn(); torch.cuda.synchronize()
@@ -44,4 +59,4 @@ for name, (fn, fl) in cases.items():
         a0.record(); fn(); a1.record(); torch.cuda.synchronize()
         ta.append(a0.elapsed_time(a1))
     ta.sort()
-    print(f"{name:10s} back-to-back {tb:.4f} ms = {fl / tb / 1e9:7.1f} TF/s | alone median {ta[len(ta) // 2]:.4f} ms = {fl / ta[len(ta) // 2] / 1e9:7.1f} TF/s (min {ta[0]:.4f})")
+    print(f"{name:10s} back-to-back {tb:.4f} ms = {fl / tb / 1e9:7.1f} TF/s | alone median {ta[len(ta) // 2]:.4f} ms = {fl / ta[len(ta) // 2] / 1e9:7.1f} TF/s (min {ta[0]:.4f}) | cuBLAS plain GEMM {cub[name]:.4f} ms -> ours/cuBLAS time {tb / cub[name]:.3f}")
