@@ -12,7 +12,7 @@ import re
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libfit_b200.so")
+LIB_PATH = os.environ.get("FITB200_LIB") or os.path.join(_PKG, "libfit_b200.so")  # FITB200_LIB: another build of the same ABI (A/B timing)
 HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "fit_b200.h")
 
 F32, BF16 = 0, 1

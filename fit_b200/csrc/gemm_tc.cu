@@ -94,8 +94,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* empty_bar = bars + STAGES;           // [STAGES]  MMA -> TMA
   uint64_t* tfull_bar = bars + 2 * STAGES;       // [2]       MMA -> epilogue
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       epilogue -> MMA
-  uint64_t* res_bar = bars + 2 * STAGES + 4;     // [2]       residual slab landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 6);
+  uint64_t* res_bar = bars + 2 * STAGES + 4;     // [4][2]    residual slab rows of lane quarter q landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_n = ceil_div(p.N, BN), tiles_m = ceil_div(p.M, TM);
@@ -115,7 +115,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
       ptx::mbar_init(&tempty_bar[s], PAIR ? 2 * (GT_EPI_THREADS / 32) : GT_EPI_THREADS);  // pair: one arrival per epilogue warp of both CTAs
-      ptx::mbar_init(&res_bar[s], 1);
+      for (int qd = 0; qd < 4; ++qd) ptx::mbar_init(&res_bar[qd * 2 + s], 1);
     }
     ptx::fence_mbar_init();
   }
@@ -207,7 +207,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
     const int half = (warp - 2) >> 2;        // which half of each slab's columns this warp handles
     const int row = quarter * 32 + lane;     // row inside the tile == TMEM lane
-    const bool leader = threadIdx.x == 64;   // first epilogue thread: issues the TMA stores / residual loads
+    // The epilogue is four independent pipelines, one per TMEM lane quarter (two warps = 64 threads, 32 tile rows): each stages, stores
+    // and prefetches the residual of ITS rows (32-row TMA boxes) behind its own named barrier, so a slow quarter never stalls the others
+    // (one 128-row store per slab behind two CTA-wide barriers kept all eight warps in lock step).
+    const bool leader = half == 0 && lane == 0;  // issues this quarter's TMA stores / residual loads
+    const int qbar = 1 + quarter;                // named barrier of this quarter's two warps
+    constexpr int QROWS = 32, QBYTES = QROWS * 128;
     const uint32_t sw = (uint32_t)(row & 7); // 128B-swizzle phase of this row
     const int my_tiles = wid < num_tiles ? (num_tiles - 1 - wid) / nwork + 1 : 0;
     const uint32_t tempty_leader = PAIR ? ptx::mapa(ptx::smem_u32(&tempty_bar[0]), 0) : 0u;  // the leader's tempty_bar[0]
@@ -218,8 +223,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (qq >= total_slabs) return;
       const int tile = wid + (qq / NSLAB) * nwork, slab = qq % NSLAB;
       const int rm0 = (tile / tiles_n) * TM + row_off, rn0 = (tile % tiles_n) * BN + slab * OUTC;
-      ptx::mbar_arrive_expect_tx(&res_bar[qq & 1], GT_SLAB_BYTES);
-      ptx::tma_load_2d(smemRes + (qq & 1) * GT_SLAB_BYTES, &tmRes, &res_bar[qq & 1], rn0, rm0);
+      ptx::mbar_arrive_expect_tx(&res_bar[quarter * 2 + (qq & 1)], QBYTES);
+      ptx::tma_load_2d(smemRes + (qq & 1) * GT_SLAB_BYTES + quarter * QBYTES, &tmRes, &res_bar[quarter * 2 + (qq & 1)], rn0, rm0 + quarter * QROWS);
     };
     if (RESID && leader) { issue_resid(0); issue_resid(1); }
 
@@ -239,14 +244,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // block are consecutive): per-thread global reads of 288-byte-strided rows were the epilogue's critical path
           const int rs = p.rope_hd + 4;
           if (m0 != rope_m0) {
-            const int q4 = p.rope_hd >> 2, total = GT_BM * q4, et = threadIdx.x - 64;
-            for (int i = et; i < total; i += GT_EPI_THREADS) {
-              const int rr = i / q4, c4 = i - rr * q4;
+            const int q4 = p.rope_hd >> 2, total = QROWS * q4, et = half * 32 + lane;  // this quarter's 32 rows, by its 64 threads
+            for (int i = et; i < total; i += 64) {
+              const int rr = quarter * QROWS + i / q4, c4 = i - (i / q4) * q4;
               const int mm = min(m0 + rr, p.M - 1), smp = mm / p.rope_tokens, tok = mm - smp * p.rope_tokens;
               const float4 v = __ldg(reinterpret_cast<const float4*>(p.rope_freqs + ((size_t)(p.rope_rows == 1 ? 0 : smp) * p.rope_tokens + tok) * p.rope_hd) + c4);
               *reinterpret_cast<float4*>(smemRope + rr * rs + c4 * 4) = v;
             }
-            rope_m0 = m0;  // visible to every epilogue thread after the first slab's named barrier
+            rope_m0 = m0;  // visible to the quarter's threads after the first slab's named barrier
           }
           rope_row = smemRope + row * rs;
         } else {
@@ -272,8 +277,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint8_t* rbuf = smemRes + buf * GT_SLAB_BYTES + row * 128;
         // the TMA store that read this staging buffer two slabs ago must have finished reading it
         if (leader) ptx::tma_store_wait_read<1>();
-        if (RESID) ptx::mbar_wait(&res_bar[buf], (q >> 1) & 1);
-        ptx::named_bar_sync(1, GT_EPI_THREADS);
+        if (RESID) ptx::mbar_wait(&res_bar[quarter * 2 + buf], (q >> 1) & 1);
+        ptx::named_bar_sync(qbar, 64);
         const bool live = nacc < p.N;  // tile-uniform: slabs beyond N are skipped (their store would be fully clipped)
         if (live) {
           constexpr int HACC = ACCC / 2;  // accumulator columns of this warp's half slab
@@ -374,9 +379,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         ptx::fence_proxy_async_smem();  // make the st.shared visible to the TMA (async proxy)
-        ptx::named_bar_sync(1, GT_EPI_THREADS);
+        ptx::named_bar_sync(qbar, 64);
         if (leader) {
-          if (live) ptx::tma_store_2d(&tmOut, smemOut + buf * GT_SLAB_BYTES, nout, m0);
+          if (live) ptx::tma_store_2d(&tmOut, smemOut + buf * GT_SLAB_BYTES + quarter * QBYTES, nout, m0 + quarter * QROWS);
           ptx::tma_store_commit();
           if (RESID) issue_resid(q + 2);  // this residual buffer has been consumed by all 128 threads
         }
@@ -439,11 +444,11 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   if (rc) return rc;
   const int outc = 128 / (int)sizeof(OutT);
   const long n_out = EPI == FITB200_EPI_SWIGLU ? a.N / 2 : a.N;
-  rc = make_tmap(&tmOut, a.out, a.out_dtype, a.M, n_out, a.ldo, GT_BM, outc);
+  rc = make_tmap(&tmOut, a.out, a.out_dtype, a.M, n_out, a.ldo, 32, outc);  // one store per lane quarter: 32 rows
   if (rc) return rc;
   tmRes = tmOut;
   if (EPI == FITB200_EPI_BIAS_GATE_RESID) {
-    rc = make_tmap(&tmRes, a.resid, a.out_dtype, a.M, a.N, a.ld_resid, GT_BM, outc);
+    rc = make_tmap(&tmRes, a.resid, a.out_dtype, a.M, a.N, a.ld_resid, 32, outc);
     if (rc) return rc;
   }
   GtParams p;

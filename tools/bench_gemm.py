@@ -27,36 +27,30 @@ cases = {
     "proj+gate": (lambda: ops.gemm(att, w_proj, b_proj, xs, EPI_BIAS_GATE_RESID, gate=gate, ld_gate=D, rows_per_sample=T, resid=xs), 2.0 * M * D * D),
 }
 scratch = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device=dev)
-# box normaliser: cuBLAS bf16 GEMMs of the same shapes (no epilogue), back to back
-cub = {}
-for nm, (A, Wt) in {"swiglu": (h, w_fc1), "qkv": (h, w_qkv), "fc2+gate": (gg, w_fc2), "proj+gate": (att, w_proj)}.items():
-    o = torch.empty(A.shape[0], Wt.shape[0], dtype=bf, device=dev)
-    for _ in range(3):
-        torch.matmul(A, Wt.t(), out=o)
-    torch.cuda.synchronize()
-    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    c0.record()
-    for _ in range(30):
-        torch.matmul(A, Wt.t(), out=o)
-    c1.record(); torch.cuda.synchronize()
-    cub[nm] = c0.elapsed_time(c1) / 30
-    del o
-cub["qkv+rope"] = cub["qkv"]
-print("pair =", os.environ.get("FITB200_GEMM_PAIR", "1"))
-for name, (fn, fl) in cases.items():
-    fn(); fn(); torch.cuda.synchronize()
-    n = 30
+# box normaliser: the cuBLAS bf16 GEMM of the same shape (no epilogue), interleaved with ours in rounds (power / thermal state drifts)
+ref = {"swiglu": (h, w_fc1), "qkv+rope": (h, w_qkv), "qkv": (h, w_qkv), "fc2+gate": (gg, w_fc2), "proj+gate": (att, w_proj)}
+
+
+def timed(fn, n=20):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(n):
         fn()
     e1.record(); torch.cuda.synchronize()
-    tb = e0.elapsed_time(e1) / n
-    ta = []
-    for _ in range(8):
-        scratch.fill_(1.0)
-        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a0.record(); fn(); a1.record(); torch.cuda.synchronize()
-        ta.append(a0.elapsed_time(a1))
-    ta.sort()
-    print(f"{name:10s} back-to-back {tb:.4f} ms = {fl / tb / 1e9:7.1f} TF/s | alone median {ta[len(ta) // 2]:.4f} ms = {fl / ta[len(ta) // 2] / 1e9:7.1f} TF/s (min {ta[0]:.4f}) | cuBLAS plain GEMM {cub[name]:.4f} ms -> ours/cuBLAS time {tb / cub[name]:.3f}")
+    return e0.elapsed_time(e1) / n
+
+
+print("pair =", os.environ.get("FITB200_GEMM_PAIR", "1"))
+for name, (fn, fl) in cases.items():
+    A, Wt = ref[name]
+    o = torch.empty(A.shape[0], Wt.shape[0], dtype=bf, device=dev)
+    cb = lambda: torch.matmul(A, Wt.t(), out=o)
+    fn(); cb(); torch.cuda.synchronize()
+    ours, cub = [], []
+    for _ in range(7):
+        cub.append(timed(cb)); ours.append(timed(fn))
+    del o
+    ratios = sorted(a / b for a, b in zip(ours, cub))
+    ours.sort(); cub.sort()
+    tb = ours[len(ours) // 2]
+    print(f"{name:10s} {tb:.4f} ms = {fl / tb / 1e9:7.1f} TF/s | cuBLAS plain GEMM {cub[len(cub) // 2]:.4f} ms | ours/cuBLAS time: median {ratios[len(ratios) // 2]:.3f} (min {ratios[0]:.3f}, max {ratios[-1]:.3f})")
