@@ -312,6 +312,9 @@ def run_cuda_arm(args):
 
 
 def main():
+    # stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION on the GPU boxes) off it
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
