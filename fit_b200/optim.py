@@ -1,0 +1,137 @@
+"""Fused AdamW + EMA optimizer step.
+
+Mirrors what the reference training loop runs after backward / all-reduce: ``torch.optim.AdamW(self.parameters(), lr=1e-4,
+weight_decay=0)`` (FiT/train.py:215-217) wrapped by the EMA optimizer (FiT/ema.py:231-278: ``step`` = optimizer step, then every
+``every_n_steps`` the EMA copy is updated with ``ema = ema * decay + p * (1 - decay)``, ema.py:149-154).  Here both are ONE CUDA
+kernel over a chunk table of all parameter tensors (``fitb200_adamw_ema_step``): p, g, m, v, ema are read once and p, m, v, ema
+written once.  Same constructor arguments and state names (``exp_avg``, ``exp_avg_sq``, ``step``) as torch.optim.AdamW; ``ema_params``,
+``swap_model_weights`` and ``swap_ema_weights`` follow FiT/ema.py:280-313.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+import math
+from typing import Iterable, List, Optional, Tuple
+
+import torch
+
+from . import _lib as L
+
+ADAM_CHUNK = 16384  # FITB200_ADAM_CHUNK
+
+
+class _AdamTensor(C.Structure):
+    """Mirror of fitb200_adam_tensor (include/fit_b200.h)."""
+    _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("ema", C.c_void_p), ("numel", C.c_int64)]
+
+
+class FusedAdamWEMA:
+    def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-4, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, ema_decay: Optional[float] = 0.9999, every_n_steps: int = 1):
+        self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
+        if not self.params:
+            raise ValueError("optimizer got an empty parameter list")
+        for p in self.params:
+            if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+                raise RuntimeError("fit_b200.optim: parameters must be contiguous fp32 CUDA tensors (no CPU fallback)")
+        if ema_decay is not None and not 0.0 <= ema_decay <= 1.0:
+            raise ValueError("Decay must be within 0 and 1")   # FiT/ema.py:47-48
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.ema_decay, self.every_n_steps = ema_decay, every_n_steps
+        self.step_count = 0
+        self.exp_avg = [torch.zeros_like(p) for p in self.params]
+        self.exp_avg_sq = [torch.zeros_like(p) for p in self.params]
+        # FiT/ema.py:243-248: the EMA copy starts as a deep copy of the parameters
+        self.ema_params = tuple(p.detach().clone() for p in self.params) if ema_decay is not None else ()
+        self._table = None
+        self._table_key = None
+
+    # ------------------------------------------------------------------ tables
+    def _build_table(self, grads: List[torch.Tensor]):
+        key = tuple(g.data_ptr() for g in grads) + tuple(p.data_ptr() for p in self.params)
+        if self._table is not None and key == self._table_key:
+            return
+        dev = self.params[0].device
+        arr = (_AdamTensor * len(self.params))()
+        chunks = []
+        for i, (p, g) in enumerate(zip(self.params, grads)):
+            arr[i].p, arr[i].g, arr[i].m, arr[i].v = p.data_ptr(), g.data_ptr(), self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr()
+            arr[i].ema = self.ema_params[i].data_ptr() if self.ema_params else 0
+            arr[i].numel = p.numel()
+            if any(int(x or 0) % 16 for x in (arr[i].p, arr[i].g, arr[i].m, arr[i].v, arr[i].ema)):
+                raise RuntimeError("fit_b200.optim: parameter / gradient / state tensors must be 16-byte aligned")
+            for first in range(0, p.numel(), ADAM_CHUNK):
+                chunks += [i, first]
+        raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone()
+        self._table = (raw.to(dev), torch.tensor(chunks, dtype=torch.int32).to(dev), len(chunks) // 2)
+        self._table_key = key
+
+    # ------------------------------------------------------------------ torch.optim-like API
+    def zero_grad(self, set_to_none: bool = False):
+        for p in self.params:
+            if p.grad is not None:
+                if set_to_none:
+                    p.grad = None
+                else:
+                    p.grad.zero_()
+
+    @torch.no_grad()
+    def step(self):
+        grads = []
+        for p in self.params:
+            if p.grad is None:
+                raise RuntimeError("fit_b200.optim: every parameter needs a gradient (the FiT step produces all of them)")
+            g = p.grad
+            if g.dtype != torch.float32 or not g.is_contiguous():
+                raise RuntimeError("fit_b200.optim: gradients must be contiguous fp32")
+            grads.append(g)
+        self._build_table(grads)
+        self.step_count += 1
+        b1, b2 = self.betas
+        bc1 = 1.0 - b1 ** self.step_count
+        bc2_sqrt = math.sqrt(1.0 - b2 ** self.step_count)
+        # FiT/ema.py:252-257: the EMA moves when (step index before increment) % every_n_steps == 0
+        do_ema = self.ema_decay is not None and (self.step_count - 1) % self.every_n_steps == 0
+        tab, chunks, n_chunks = self._table
+        L.check(L.lib().fitb200_adamw_ema_step(L.ptr(tab), L.ptr(chunks), n_chunks, self.lr, b1, b2, self.eps, self.weight_decay, bc1, bc2_sqrt,
+                                               self.ema_decay if do_ema else -1.0, L.stream_ptr()), "adamw_ema_step")
+        self.bump_versions()
+
+    def bump_versions(self):
+        """The kernel wrote the parameters behind autograd's back: bump their version counters so that the weight caches keyed by
+        (data_ptr, _version) (fit_b200.engine._Weights) repack."""
+        torch._C._autograd._unsafe_set_version_counter(tuple(self.params), tuple(p._version + 1 for p in self.params))
+
+    # ------------------------------------------------------------------ EMA helpers (FiT/ema.py:280-313)
+    def swap_ema_weights(self):
+        for p, e in zip(self.params, self.ema_params):
+            tmp = p.data.clone()
+            p.data.copy_(e)
+            e.copy_(tmp)
+        self.bump_versions()
+
+    @contextlib.contextmanager
+    def swap_ema_weights_ctx(self, enabled: bool = True):
+        if enabled:
+            self.swap_ema_weights()
+        try:
+            yield
+        finally:
+            if enabled:
+                self.swap_ema_weights()
+
+    def state_dict(self):
+        return {"state": {i: {"step": torch.tensor(float(self.step_count)), "exp_avg": m, "exp_avg_sq": v}
+                          for i, (m, v) in enumerate(zip(self.exp_avg, self.exp_avg_sq))},
+                "param_groups": [{"lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay,
+                                  "params": list(range(len(self.params)))}],
+                "ema": self.ema_params, "current_step": self.step_count, "decay": self.ema_decay, "every_n_steps": self.every_n_steps}
+
+    def load_state_dict(self, sd):
+        for i, st in sd["state"].items():
+            self.exp_avg[int(i)].copy_(st["exp_avg"]); self.exp_avg_sq[int(i)].copy_(st["exp_avg_sq"])
+        self.step_count = int(sd.get("current_step", 0))
+        if sd.get("ema") is not None and self.ema_params:
+            for e, src in zip(self.ema_params, sd["ema"]):
+                e.copy_(src)

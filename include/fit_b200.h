@@ -238,6 +238,28 @@ int fitb200_masked_mse_fwd(const float* out, const float* target, const uint8_t*
 int fitb200_masked_mse_bwd(const float* out, const float* target, const uint8_t* mask, int64_t tokens, int P, const float* acc,
                            const float* gscale, void* dout, int dout_dtype, fitb200_stream_t stream);
 
+
+/* ---- optimizer step: torch.optim.AdamW(lr=1e-4, weight_decay=0) (FiT/train.py:215-217) followed by the
+ * EMA update ema = ema * decay + p * (1 - decay) (FiT/ema.py:149-154,256-267) as ONE multi-tensor pass over (p, g, m, v, ema).
+ * Per element, in torch's single-tensor AdamW order:  p *= 1 - lr * wd;  m += (g - m) * (1 - beta1);  v = v * beta2 + g * g * (1 - beta2);
+ * p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)   with bc1 = 1 - beta1^t, bc2 = 1 - beta2^t computed by the caller in double.
+ * tensors: device array of n_tensors descriptors; chunks: device array of n_chunks {tensor index, first element} pairs, every chunk
+ * covers FITB200_ADAM_CHUNK elements (the last chunk of a tensor is cut by numel).  ema may be null per tensor (no EMA) and
+ * ema_decay < 0 skips the EMA update of this step (every_n_steps).  All buffers fp32, 16-byte aligned.  36 B per element.
+ * Hyper-parameters are doubles: torch forms 1 - beta, lr / bc1, 1 - decay in double before the fp32 arithmetic, and so does this. */
+#define FITB200_ADAM_CHUNK 16384
+typedef struct fitb200_adam_tensor {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  float* ema;
+  int64_t numel;
+} fitb200_adam_tensor;
+int fitb200_adamw_ema_step(const fitb200_adam_tensor* tensors, const int32_t* chunks, int n_chunks, double lr, double beta1, double beta2,
+                           double eps, double weight_decay, double bias_correction1, double bias_correction2_sqrt, double ema_decay,
+                           fitb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
