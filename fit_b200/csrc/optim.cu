@@ -1,4 +1,5 @@
-// Fused multi-tensor AdamW + EMA step.  Replaces torch.optim.AdamW.step (FiT/train.py:215-217) and the EMA
+// Training-loop neighbours of the hot path.
+// (1) Fused multi-tensor AdamW + EMA step (row f3).  Replaces torch.optim.AdamW.step (FiT/train.py:215-217) and the EMA
 // wrapper's _foreach_mul_ / _foreach_add_ pair on a side stream (FiT/ema.py:149-154,256-267) by ONE pass: every element of
 // (p, g, m, v, ema) is read once and (p, m, v, ema) written once -- 36 B per element, HBM-bound (FiT-XL/2: 674.9 M elements = 24.3 GB).
 // One CTA = one FITB200_ADAM_CHUNK-element chunk of one tensor (chunk table built once by the host), 16-byte accesses, grid = chunks.
@@ -51,9 +52,42 @@ __global__ void __launch_bounds__(256) adamw_ema_kernel(const fitb200_adam_tenso
   }
 }
 
+// masked_FiT token sub-sampling + RoPE row gather (row f4): one warp per output token, lanes copy the P latent and d RoPE floats.
+__global__ void __launch_bounds__(256) subsample_tokens_kernel(const float* __restrict__ latent, const float* __restrict__ pos,
+                                                               const uint8_t* __restrict__ mask, const int64_t* __restrict__ perm,
+                                                               const int32_t* __restrict__ n_tokens, int Tsrc, int P, int d, int Tout,
+                                                               float* __restrict__ latent_out, float* __restrict__ pos_out,
+                                                               uint8_t* __restrict__ mask_out) {
+  const int s = blockIdx.y, j = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (j >= Tout) return;
+  const int nt = min(n_tokens[s], Tsrc);
+  long src = -1;  // source token, -1 = padding
+  if (nt > Tout) {
+    src = perm[(size_t)s * Tsrc + j];
+    if (src < 0 || src >= nt) src = -1;  // a malformed permutation yields padding instead of an out-of-bounds read
+  } else if (j < nt) {
+    src = j;
+  }
+  const size_t so = (size_t)s * Tsrc + (src < 0 ? 0 : src), oo = (size_t)s * Tout + j;
+  for (int i = lane; i < P; i += 32) latent_out[oo * P + i] = src < 0 ? 0.f : latent[so * P + i];
+  for (int i = lane; i < d; i += 32) pos_out[oo * d + i] = src < 0 ? 0.f : pos[so * d + i];
+  if (lane == 0) mask_out[oo] = src < 0 ? (uint8_t)0 : mask[so];
+}
+
 }  // namespace fitb200
 
 using namespace fitb200;
+
+extern "C" int fitb200_subsample_tokens(const float* latent, const float* pos, const uint8_t* mask, const int64_t* perm, const int32_t* n_tokens, int N,
+                                        int Tsrc, int P, int d, int Tout, float* latent_out, float* pos_out, uint8_t* mask_out,
+                                        fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(latent && pos && mask && perm && n_tokens && latent_out && pos_out && mask_out, "subsample_tokens: null pointer");
+  FITB200_CHECK_ARG(N > 0 && Tsrc > 0 && P > 0 && d > 0 && Tout > 0 && N <= 65535, "subsample_tokens: bad sizes (N=%d Tsrc=%d P=%d d=%d Tout=%d)", N, Tsrc, P, d, Tout);
+  dim3 grid((unsigned)ceil_div(Tout, 8), (unsigned)N);
+  subsample_tokens_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(latent, pos, mask, perm, n_tokens, Tsrc, P, d, Tout, latent_out, pos_out, mask_out);
+  FITB200_CHECK_LAUNCH("subsample_tokens");
+  return FITB200_OK;
+}
 
 extern "C" int fitb200_adamw_ema_step(const fitb200_adam_tensor* tensors, const int32_t* chunks, int n_chunks, double lr, double beta1, double beta2,
                                       double eps, double weight_decay, double bias_correction1, double bias_correction2_sqrt, double ema_decay,

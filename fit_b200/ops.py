@@ -310,3 +310,20 @@ def masked_mse_bwd(out: Tensor, target: Tensor, mask: Tensor, acc: Tensor, gscal
     L.check(L.lib().fitb200_masked_mse_bwd(L.ptr(_c(out)), L.ptr(_c(target)), L.ptr(_m8(mask)), mask.numel(), P, L.ptr(acc), L.ptr(gscale),
                                            L.ptr(dout), L.dtype_code(dout), L.stream_ptr()), "masked_mse_bwd")
     return dout
+
+
+def subsample_tokens(latent: Tensor, pos: Tensor, mask: Tensor, perm: Tensor, n_tokens: Tensor, number_of_tokens: int):
+    """masked_FiT subsample + collate on device (masked_FiT/preprocess/iterators.py:142-169): latent [N,Tsrc,P] fp32, pos [N,Tsrc,d] fp32,
+    mask [N,Tsrc] bool, perm [N,Tsrc] int64 (host-drawn randperm of range(n_tokens[s]), unused where n_tokens[s] <= T'), n_tokens [N] int32.
+    Returns (latent [N,T',P], pos [N,T',d], mask [N,T'] bool)."""
+    L.require_cuda(latent, pos, mask, perm, n_tokens)
+    N, Tsrc, P = latent.shape
+    d = pos.shape[2]
+    assert pos.shape[:2] == (N, Tsrc) and mask.shape == (N, Tsrc) and perm.shape == (N, Tsrc) and n_tokens.shape == (N,)
+    assert latent.dtype == torch.float32 and pos.dtype == torch.float32 and perm.dtype == torch.int64 and n_tokens.dtype == torch.int32
+    lo = torch.empty(N, number_of_tokens, P, dtype=torch.float32, device=latent.device)
+    po = torch.empty(N, number_of_tokens, d, dtype=torch.float32, device=latent.device)
+    mo = torch.empty(N, number_of_tokens, dtype=torch.bool, device=latent.device)
+    L.check(L.lib().fitb200_subsample_tokens(L.ptr(_c(latent)), L.ptr(_c(pos)), L.ptr(_m8(mask)), L.ptr(_c(perm)), L.ptr(n_tokens), N, Tsrc, P, d,
+                                             number_of_tokens, L.ptr(lo), L.ptr(po), L.ptr(mo), L.stream_ptr()), "subsample_tokens")
+    return lo, po, mo

@@ -239,6 +239,16 @@ int fitb200_masked_mse_bwd(const float* out, const float* target, const uint8_t*
                            const float* gscale, void* dout, int dout_dtype, fitb200_stream_t stream);
 
 
+/* ---- masked_FiT token sub-sampling: ImageNetLatentIterator.subsample / collate
+ * (masked_FiT/preprocess/iterators.py:142-169) for a whole batch in one launch.  Sample s holds n_tokens[s] valid tokens in
+ * latent[s, :, :P], pos[s, :, :d] (d = RoPE row width) and mask[s, :] (bytes).  With T' = Tout:
+ *   n_tokens[s] >  T': out[s, j] = in[s, perm[s, j]] for j < T'  (random subset in permuted order, iterators.py:143-148; the
+ *                      permutation is an INPUT -- torch.randperm stays on the host for RNG parity with the reference);
+ *   n_tokens[s] <= T': out[s, j] = in[s, j] for j < n_tokens[s], zeros (mask False) behind (iterators.py:150-154, no permutation).
+ * Bit-exact copies.  perm: int64 [N, Tsrc]; latent_out [N, T', P], pos_out [N, T', d] fp32, mask_out [N, T'] bytes. */
+int fitb200_subsample_tokens(const float* latent, const float* pos, const uint8_t* mask, const int64_t* perm, const int32_t* n_tokens, int N,
+                             int Tsrc, int P, int d, int Tout, float* latent_out, float* pos_out, uint8_t* mask_out, fitb200_stream_t stream);
+
 /* ---- optimizer step: torch.optim.AdamW(lr=1e-4, weight_decay=0) (FiT/train.py:215-217) followed by the
  * EMA update ema = ema * decay + p * (1 - decay) (FiT/ema.py:149-154,256-267) as ONE multi-tensor pass over (p, g, m, v, ema).
  * Per element, in torch's single-tensor AdamW order:  p *= 1 - lr * wd;  m += (g - m) * (1 - beta1);  v = v * beta2 + g * g * (1 - beta2);

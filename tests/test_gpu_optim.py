@@ -61,3 +61,20 @@ def test_swap_ema_weights_roundtrip():
     with opt.swap_ema_weights_ctx():
         assert torch.equal(p.detach(), ema)
     assert torch.equal(p.detach(), before) and torch.equal(opt.ema_params[0], ema)
+
+
+@pytest.mark.parametrize("number_of_tokens", [32, 96, 256])
+def test_masked_subsample_matches_reference_collate(number_of_tokens):
+    """masked_FiT subsample / collate on device (row f4) vs the CPU restatement, same RNG stream: bit-exact."""
+    from fit_b200.masked import subsample_batch
+    from oracle.subsample_oracle import collate
+    g = torch.Generator().manual_seed(7)
+    sizes = [256, 200, 96, 32, 31, 1, 160, 97]      # over-long, exact, shorter than every choice, ragged
+    lat = [torch.randn(n, 16, generator=g) for n in sizes]
+    pos = [torch.randn(n, 72, generator=g) for n in sizes]
+    msk = [torch.ones(n, dtype=torch.bool) for n in sizes]
+    msk[1][5] = False                                # mask bytes travel with their tokens
+    want = collate(lat, pos, msk, number_of_tokens, generator=torch.Generator().manual_seed(11))
+    got = subsample_batch(lat, pos, msk, number_of_tokens, "cuda", generator=torch.Generator().manual_seed(11))
+    for w, o in zip(want, got):
+        assert o.shape == w.shape and torch.equal(o.cpu(), w)
