@@ -133,3 +133,72 @@ def shard_rows(total: int, world: int, rank: int) -> Tuple[int, int]:
     base, rem = divmod(total, world)
     begin = rank * base + min(rank, rem)
     return begin, begin + base + (1 if rank < rem else 0)
+
+
+# ---------------------------------------------------------------------------------------------------- batch driver (row f1)
+class SamplingDriver:
+    """The batch loop of sample_lightning.py:26-70 on top of CFGSampler.
+
+    Per batch the reference draws labels (``torch.randint``) and latents (``torch.randn``), pads the latent tokens to 256
+    (``_pad_latent``), builds the RoPE table / mask for the resolution (``_create_pos_embed`` / ``_create_mask``), runs
+    ``ddim_sample_loop(model.forward_with_cfg, ...)`` on 2B rows, keeps the first half and un-pads it.  Here the network runs
+    on the latent's own token count (padded key tokens are masked out in the reference, so they change nothing for the valid
+    ones), the RoPE table of a resolution is built once and cached (``rope.create_pos_embed``, VisionNTK included), and
+    there is one CUDA-graph sampler per (batch size, latent height, latent width) bucket.  With ``world`` > 1 every rank takes
+    its ``shard_rows`` slice of each batch (no collective); the noise is keyed by the global image index.
+    VAE decoding (sample_lightning.py:72-74) is out of scope: the method returns latents."""
+
+    def __init__(self, model, diffusion, cfg_scale: float = 1.5, mode: str = "ddim", eta: float = 0.0, seed: int = 0, max_length: int = 256,
+                 rank: int = 0, world: int = 1, max_buckets: int = 4):
+        self.model, self.diffusion = model, diffusion
+        self.cfg_scale, self.mode, self.eta, self.seed, self.max_length = cfg_scale, mode, eta, seed, max_length
+        self.rank, self.world, self.max_buckets = rank, world, max_buckets
+        self._samplers = {}
+        self._pos = {}
+
+    def _pos_table(self, h: int, w: int) -> Tensor:
+        key = (h, w)
+        if key not in self._pos:
+            from .rope import create_pos_embed
+            m = self.model
+            table, valid_t = create_pos_embed(h, w, m.patch_size, self.max_length, m.hidden_size // m.num_heads)
+            self._pos[key] = table[:, :valid_t].contiguous().pin_memory()
+        return self._pos[key]
+
+    def _sampler(self, B: int, h: int, w: int, row_offset: int) -> CFGSampler:
+        key = (B, h, w)
+        s = self._samplers.get(key)
+        if s is None:
+            if len(self._samplers) >= self.max_buckets:
+                self._samplers.pop(next(iter(self._samplers)))
+            s = CFGSampler(self.model, self.diffusion, batch=B, latent_hw=(h, w), cfg_scale=self.cfg_scale, seed=self.seed, mode=self.mode,
+                           eta=self.eta)
+            self._samplers[key] = s
+        s.row_offset = row_offset   # read at launch time by the noise kernel: part of the captured arguments, so re-capture
+        return s
+
+    def sample(self, num_samples: int, image_hw: Tuple[int, int], batch_size: int = 100, num_classes: int = 1000,
+               generator: Optional[torch.Generator] = None, labels: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
+        """Returns (latents [n_local, C, H/8, W/8] on the device, labels [n_local]) of this rank's share of ``num_samples`` images."""
+        H, W = image_hw[0] // 8, image_hw[1] // 8                   # sample_lightning.py:35
+        C = self.model.in_channels
+        pos = self._pos_table(H, W)
+        outs, labs = [], []
+        done = 0
+        while done < num_samples:
+            cur = min(batch_size, num_samples - done)               # sample_lightning.py:32
+            y_all = torch.randint(0, num_classes, (cur,), generator=generator) if labels is None else labels[done:done + cur].cpu()
+            z_all = torch.randn(cur, C, H, W, generator=generator)  # host draw (the reference draws on its device generator)
+            b0, b1 = shard_rows(cur, self.world, self.rank)
+            if b1 > b0:
+                s = self._sampler(b1 - b0, H, W, row_offset=done + b0)
+                if s._graph is not None and getattr(s, "_captured_offset", None) != s.row_offset:
+                    s._graph = None                                  # the noise key (global image index) is a captured scalar
+                s._captured_offset = s.row_offset
+                outs.append(s.sample(z_all[b0:b1].pin_memory(), y_all[b0:b1].to(torch.int64).pin_memory(), pos))
+                labs.append(y_all[b0:b1])
+            done += cur
+        dev = next(self.model.parameters()).device
+        if not outs:
+            return torch.empty(0, C, H, W, device=dev), torch.empty(0, dtype=torch.int64)
+        return torch.cat(outs), torch.cat(labs)
