@@ -27,33 +27,48 @@ __global__ void gate_resid_fwd_kernel(const T* __restrict__ resid, const T* __re
 }
 
 // ------------------------------------------------------------------------------------------------ gate backward
-// dy = gate[s] * dx;  dgate[s, :] += sum_t dx * y;  dbias[:] += sum_m dy.   grid = (col groups, samples, token chunks)
+// dy = gate[s] * dx;  dgate[s, :] += sum_t dx * y;  dbias[:] += sum_m dy.
+// One CTA = (256 columns, one sample, ALL its rows): 32 column groups of 8 x 8 row lanes; the row lanes are reduced through shared
+// memory, so dgate needs no atomics at all and dbias one per (sample, column).  (The first version split the rows into chunks that
+// each ended in atomicAdds on the same addresses: 2.4 ms per XL/2 step, and 4.7 ms with three times the chunks.)
+constexpr int CR_LANES = 8;   // row lanes per CTA of the column-reduction kernels
 template <typename T>
-__global__ void gate_bwd_kernel(const T* __restrict__ dx, const T* __restrict__ y, const float* __restrict__ gate, long ld_gate, int D,
-                                int rps, int rows_per_chunk, T* __restrict__ dy, float* __restrict__ dgate, long ld_dgate,
-                                float* __restrict__ dbias) {
-  const int cg = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cg >= (D >> 3)) return;
-  const int c = cg * 8, s = blockIdx.y;
-  const int t0 = blockIdx.z * rows_per_chunk, t1 = min(rps, t0 + rows_per_chunk);
-  const Vec8<float> g = Vec8<float>::load(gate + (size_t)s * ld_gate + c);
+__global__ void __launch_bounds__(256) gate_bwd_kernel(const T* __restrict__ dx, const T* __restrict__ y, const float* __restrict__ gate,
+                                                       long ld_gate, int D, int rps, T* __restrict__ dy, float* __restrict__ dgate,
+                                                       long ld_dgate, float* __restrict__ dbias) {
+  __shared__ float red[CR_LANES][32][17];
+  const int cgl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int cg = blockIdx.x * 32 + cgl, c = cg * 8, s = blockIdx.y;
+  const bool live = cg < (D >> 3);
   float ag[8] = {}, ab[8] = {};
-  for (int t = t0; t < t1; ++t) {
-    const size_t off = ((size_t)s * rps + t) * D + c;
-    const Vec8<T> d = Vec8<T>::load(dx + off), yy = Vec8<T>::load(y + off);
-    Vec8<T> o;
+  if (live) {
+    const Vec8<float> g = Vec8<float>::load(gate + (size_t)s * ld_gate + c);
+#pragma unroll 4
+    for (int t = rl; t < rps; t += CR_LANES) {
+      const size_t off = ((size_t)s * rps + t) * D + c;
+      const Vec8<T> d = Vec8<T>::load(dx + off), yy = Vec8<T>::load(y + off);
+      Vec8<T> o;
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      ag[e] = fmaf(d.v[e], yy.v[e], ag[e]);
-      o.v[e] = g.v[e] * d.v[e];
-      ab[e] += o.v[e];
+      for (int e = 0; e < 8; ++e) {
+        ag[e] = fmaf(d.v[e], yy.v[e], ag[e]);
+        o.v[e] = g.v[e] * d.v[e];
+        ab[e] += o.v[e];
+      }
+      o.store(dy + off);
     }
-    o.store(dy + off);
   }
 #pragma unroll
-  for (int e = 0; e < 8; ++e) {
-    atomicAdd(dgate + (size_t)s * ld_dgate + c + e, ag[e]);
-    if (dbias) atomicAdd(dbias + c + e, ab[e]);
+  for (int e = 0; e < 8; ++e) { red[rl][cgl][e] = ag[e]; red[rl][cgl][8 + e] = ab[e]; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 32 * 16; i += 256) {
+    const int g2 = i >> 4, e = i & 15, col = (blockIdx.x * 32 + g2) * 8 + (e & 7);
+    if (col < D) {
+      float v = 0.f;
+#pragma unroll
+      for (int r = 0; r < CR_LANES; ++r) v += red[r][g2][e];
+      if (e < 8) dgate[(size_t)s * ld_dgate + col] += v;   // this CTA owns (sample, column): plain read-modify-write
+      else if (dbias) atomicAdd(dbias + col, v);
+    }
   }
 }
 
@@ -83,6 +98,7 @@ __global__ void swiglu_bwd_kernel(const T* __restrict__ dg, const T* __restrict_
   const int m0 = blockIdx.y * rows_per_chunk, m1 = min(M, m0 + rows_per_chunk);
   const int uc = (j >> 1) * 32 + (j & 1) * 8;
   float sa[8] = {}, sb[8] = {};
+#pragma unroll 4
   for (int m = m0; m < m1; ++m) {
     const size_t uo = (size_t)m * 2 * Hp + uc;
     const Vec8<T> a = Vec8<T>::load(u + uo), b = Vec8<T>::load(u + uo + 16), d = Vec8<T>::load(dg + (size_t)m * Hp + j * 8);
@@ -147,27 +163,38 @@ __global__ void __launch_bounds__(256) ln_bwd_rows_kernel(const T* __restrict__ 
   }
 }
 
-// columns: dshift[s, :] += sum_t dh;  dscale[s, :] += sum_t dh * xhat.   grid = (col groups, samples, token chunks)
+// columns: dshift[s, :] += sum_t dh;  dscale[s, :] += sum_t dh * xhat.   Same CTA shape as gate_bwd_kernel: no atomics.
 template <typename T>
-__global__ void mod_bwd_cols_kernel(const T* __restrict__ dh, const T* __restrict__ x, const float* __restrict__ mean,
-                                    const float* __restrict__ rstd, int D, int rps, int rows_per_chunk, float* __restrict__ dshift,
-                                    float* __restrict__ dscale, long ld_mod) {
-  const int cg = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cg >= (D >> 3)) return;
-  const int c = cg * 8, s = blockIdx.y;
-  const int t0 = blockIdx.z * rows_per_chunk, t1 = min(rps, t0 + rows_per_chunk);
+__global__ void __launch_bounds__(256) mod_bwd_cols_kernel(const T* __restrict__ dh, const T* __restrict__ x, const float* __restrict__ mean,
+                                                           const float* __restrict__ rstd, int D, int rps, float* __restrict__ dshift,
+                                                           float* __restrict__ dscale, long ld_mod) {
+  __shared__ float red[CR_LANES][32][17];
+  const int cgl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int cg = blockIdx.x * 32 + cgl, c = cg * 8, s = blockIdx.y;
+  const bool live = cg < (D >> 3);
   float a1[8] = {}, a2[8] = {};
-  for (int t = t0; t < t1; ++t) {
-    const size_t row = (size_t)s * rps + t;
-    const float mu = mean[row], rs = rstd[row];
-    const Vec8<T> d = Vec8<T>::load(dh + row * D + c), a = Vec8<T>::load(x + row * D + c);
+  if (live) {
+#pragma unroll 4
+    for (int t = rl; t < rps; t += CR_LANES) {
+      const size_t row = (size_t)s * rps + t;
+      const float mu = mean[row], rs = rstd[row];
+      const Vec8<T> d = Vec8<T>::load(dh + row * D + c), a = Vec8<T>::load(x + row * D + c);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { a1[e] += d.v[e]; a2[e] = fmaf(d.v[e], (a.v[e] - mu) * rs, a2[e]); }
+      for (int e = 0; e < 8; ++e) { a1[e] += d.v[e]; a2[e] = fmaf(d.v[e], (a.v[e] - mu) * rs, a2[e]); }
+    }
   }
 #pragma unroll
-  for (int e = 0; e < 8; ++e) {
-    atomicAdd(dshift + (size_t)s * ld_mod + c + e, a1[e]);
-    atomicAdd(dscale + (size_t)s * ld_mod + c + e, a2[e]);
+  for (int e = 0; e < 8; ++e) { red[rl][cgl][e] = a1[e]; red[rl][cgl][8 + e] = a2[e]; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 32 * 16; i += 256) {
+    const int g2 = i >> 4, e = i & 15, col = (blockIdx.x * 32 + g2) * 8 + (e & 7);
+    if (col < D) {
+      float v = 0.f;
+#pragma unroll
+      for (int r = 0; r < CR_LANES; ++r) v += red[r][g2][e];
+      float* dst = (e < 8 ? dshift : dscale) + (size_t)s * ld_mod + col;
+      *dst += v;
+    }
   }
 }
 
@@ -178,6 +205,7 @@ __global__ void colsum_kernel(const T* __restrict__ a, int M, int N, long lda, i
   if (n >= N) return;
   const int m0 = blockIdx.y * rows_per_chunk, m1 = min(M, m0 + rows_per_chunk);
   float s = 0.f;
+#pragma unroll 8
   for (int m = m0; m < m1; ++m) s += to_f32(a[(size_t)m * lda + n]);
   atomicAdd(out + n, s);
 }
@@ -250,7 +278,9 @@ static inline int grid_for(long n, int block, int cap = 148 * 16) {
   long g = (n + block - 1) / block;
   return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
-static inline int chunk_rows(int rows, long other_ctas) {  // enough CTAs for ~4 waves without tiny chunks
+// enough CTAs for ~4 waves without tiny chunks.  More, smaller chunks were measured slower (gate_bwd 2.4 -> 4.7 ms per XL/2 step): every
+// chunk ends in atomicAdds on the same dgate / dbias addresses, and those, not the row loop, bound these kernels.
+static inline int chunk_rows(int rows, long other_ctas) {
   int chunks = (int)((148L * 4 + other_ctas - 1) / other_ctas);
   if (chunks < 1) chunks = 1;
   int rpc = (rows + chunks - 1) / chunks;
@@ -279,11 +309,9 @@ int fitb200_gate_resid_fwd(const void* resid, const void* y, int dtype, const fl
 int fitb200_gate_bwd(const void* dx, const void* y, int dtype, const float* gate, int64_t ld_gate, int R, int rows_per_sample, int D,
                      void* dy, float* dgate, int64_t ld_dgate, float* dbias, fitb200_stream_t stream) {
   FITB200_CHECK_ARG(dx && y && gate && dy && dgate && R > 0 && rows_per_sample > 0 && D % 8 == 0 && ld_gate % 4 == 0, "gate_bwd: bad arguments");
-  const int bx = ceil_div(D / 8, 128);
-  const int rpc = chunk_rows(rows_per_sample, (long)bx * R);
-  dim3 grid(bx, R, ceil_div(rows_per_sample, rpc));
+  dim3 grid(ceil_div(D / 8, 32), R);
   FITB200_DISPATCH_ACT(dtype, T, {
-    gate_bwd_kernel<T><<<grid, 128, 0, BW_STREAM>>>((const T*)dx, (const T*)y, gate, ld_gate, D, rows_per_sample, rpc, (T*)dy, dgate, ld_dgate, dbias);
+    gate_bwd_kernel<T><<<grid, 256, 0, BW_STREAM>>>((const T*)dx, (const T*)y, gate, ld_gate, D, rows_per_sample, (T*)dy, dgate, ld_dgate, dbias);
   })
   FITB200_CHECK_LAUNCH("gate_bwd");
   return FITB200_OK;
@@ -322,11 +350,9 @@ int fitb200_ln_modulate_bwd(const void* dh, const void* x, int dtype, const floa
   FITB200_CHECK_LAUNCH("ln_bwd_rows");
   if (dshift && dscale) {
     const int R = M / rows_per_sample;
-    const int bx = ceil_div(D / 8, 128);
-    const int rpc = chunk_rows(rows_per_sample, (long)bx * R);
-    dim3 grid(bx, R, ceil_div(rows_per_sample, rpc));
+    dim3 grid(ceil_div(D / 8, 32), R);
     FITB200_DISPATCH_ACT(dtype, T, {
-      mod_bwd_cols_kernel<T><<<grid, 128, 0, BW_STREAM>>>((const T*)dh, (const T*)x, mean, rstd, D, rows_per_sample, rpc, dshift, dscale, ld_dmod);
+      mod_bwd_cols_kernel<T><<<grid, 256, 0, BW_STREAM>>>((const T*)dh, (const T*)x, mean, rstd, D, rows_per_sample, dshift, dscale, ld_dmod);
     })
     FITB200_CHECK_LAUNCH("mod_bwd_cols");
   }
