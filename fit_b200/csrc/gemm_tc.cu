@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GtParams p) {
   using Cfg = GtCfg<BN, EPI, PAIR>;
-  static_assert(!PAIR || (!AMN && !BMN), "pair tiles: K-major operands only");
+  static_assert(!PAIR || !BMN || Cfg::BNL % 64 == 0, "pair tiles with a contraction-major B: whole 64-column boxes per CTA");
   constexpr int STAGES = Cfg::STAGES;
   constexpr int TM = PAIR ? 2 * GT_BM : GT_BM;  // rows of one scheduled tile (both CTAs of a pair)
   constexpr int NGRAN = PAIR ? 32 : 16;         // granularity of the last column tile's MMA N
@@ -143,8 +143,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // both CTAs' bytes are counted on the LEADER's full barrier (the only one the MMA thread waits on)
             if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
             const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
-            ptx::tma_load_2d_pair(smemA + stage * Cfg::A_BYTES, &tmA, fb, kb * GT_BK, m0);
-            ptx::tma_load_2d_pair(smemB + stage * Cfg::B_BYTES, &tmB, fb, kb * GT_BK, n0);
+            if (AMN) {
+#pragma unroll
+              for (int b = 0; b < GT_BM / 64; ++b) ptx::tma_load_2d_pair(smemA + stage * Cfg::A_BYTES + b * 8192, &tmA, fb, m0 + b * 64, kb * GT_BK);
+            } else {
+              ptx::tma_load_2d_pair(smemA + stage * Cfg::A_BYTES, &tmA, fb, kb * GT_BK, m0);
+            }
+            if (BMN) {
+#pragma unroll
+              for (int b = 0; b < Cfg::BNL / 64; ++b) ptx::tma_load_2d_pair(smemB + stage * Cfg::B_BYTES + b * 8192, &tmB, fb, n0 + b * 64, kb * GT_BK);
+            } else {
+              ptx::tma_load_2d_pair(smemB + stage * Cfg::B_BYTES, &tmB, fb, kb * GT_BK, n0);
+            }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
             continue;
           }
@@ -191,7 +201,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int k = 0; k < GT_BK / 16; ++k) {
             // 16 elements along K: K-major = 32 bytes inside the 128-byte swizzle row (+2 in the addr >> 4 field);
             // MN-major = 16 k-rows of 128 bytes (+128)
-            if (PAIR) ptx::mma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            if (PAIR) ptx::mma_f16_ss_pair(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0);
             else ptx::mma_f16_ss(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0);
           }
           // smem slot reusable once these MMAs retire (pair: the slot of BOTH CTAs)
@@ -488,6 +498,12 @@ template <int BN, typename OutT>
 static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
   if (a.a_mn || a.b_mn) {  // backward GEMMs: plain (optional bias) epilogue only
     if (a.epilogue != FITB200_EPI_BIAS) { set_last_error("gemm_bf16_tc: a_mn / b_mn support FITB200_EPI_BIAS only"); return FITB200_ERR_UNSUPPORTED; }
+    static const bool pair_mn = [] { const char* e = getenv("FITB200_GEMM_PAIR_MN"); return !(e && e[0] == '0'); }();
+    if constexpr (BN != 192) if (pair_mn && a.M > GT_BM) {
+      if (a.a_mn && a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, true, true>(a, s);
+      if (a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, true, true>(a, s);
+      return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, false, true>(a, s);
+    }
     if (a.a_mn && a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, true>(a, s);
     if (a.b_mn) return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, true>(a, s);
     return launch_tc<BN, FITB200_EPI_BIAS, OutT, true, false>(a, s);
