@@ -152,6 +152,34 @@ def randomize_zero_init(model, seed=1):
             p.data.copy_(torch.randn(p.shape, generator=g) * 0.02)
 
 
+def ncu_traffic(tag="r1e"):
+    """DRAM bytes (read + write) per launch of the block kernels from the committed `ncu --set full` capture of tools/prof_kernels.py at
+    the same shape (profiles/<tag>_ncu_full_block_kernels.csv); {} when the summary is absent."""
+    import csv
+    path = os.path.join(ROOT, "profiles", f"{tag}_ncu_full_block_kernels.csv")
+    if not os.path.exists(path):
+        return {}
+    out, gate_seen = {}, 0
+    with open(path) as fh:
+        rows = list(csv.reader(fh))
+    hdr = rows[0]
+    ir, iw = [i for i, h in enumerate(hdr) if h.startswith("dram_read")][0], [i for i, h in enumerate(hdr) if h.startswith("dram_write")][0]
+    scale = lambda h: 1e9 if "Gbyte" in h else 1e6 if "Mbyte" in h else 1e3 if "Kbyte" in h else 1.0  # noqa: E731
+    for r in rows[1:]:
+        name, b = r[0], float(r[ir]) * scale(hdr[ir]) + float(r[iw]) * scale(hdr[iw])
+        key = None
+        if name.startswith("gemm_tc_kernel<256, 3"): key = "gemm_tc[swiglu fc1_g|fc1_x]"
+        elif name.startswith("gemm_tc_kernel<256, 4"): key = "gemm_tc[qkv+rope]"
+        elif name.startswith("gemm_tc_kernel<256, 2"):
+            key = "gemm_tc[proj+gate+resid]" if gate_seen == 0 else "gemm_tc[fc2+gate+resid]"
+            gate_seen += 1
+        elif name.startswith("attn_tc"): key = "attn_tc[softmax(qk^T)v]"
+        elif name.startswith("ln_modulate"): key = "ln_modulate"
+        if key and key not in out:
+            out[key] = b
+    return out
+
+
 def time_kernel(fn, iters, flush):
     import torch
     fn(); fn()
@@ -208,6 +236,10 @@ def kernel_rooflines(model, sampler, peaks, iters=5):
     nel = sampler.x.numel()
     add("cfg_ddpm_step", lambda: ops.cfg_step(sampler.x, sampler.raw, sampler.noise, sampler.t_idx[: sampler.B], tb["coef"], cfg_pairs=sampler.B,
                                               cfg_scale=1.5, sample=sampler.x), 0.0, nel * 4 * 5)
+    for k, b in ncu_traffic().items():
+        if k in res:
+            res[k]["traffic"] = b
+            res[k]["traffic_source"] = "profiles/r1e_ncu_full_block_kernels.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
     return res
 
 

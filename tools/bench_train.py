@@ -9,7 +9,7 @@ from fit_b200.rope import precompute_freqs_cis_2d
 from fit_b200.train import masked_mse_loss
 
 name = os.environ.get("MODEL", "FiT-XL/2")
-N, T = int(os.environ.get("BATCH", 32)), 256
+N, T = int(os.environ.get("BATCH", 32)), int(os.environ.get("TOK", 256))
 valid = int(os.environ.get("VALID", T))
 D, Hd, L, heads = bench.MODELS[name]
 torch.manual_seed(0)
