@@ -115,11 +115,11 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const int row0 = r * Tn, cq = head * CH, ck = (D + head * HD) / 8, cv = (2 * D + head * HD) / 8;
         for (int qt = 0; qt < nlive; ++qt, ++uq) {
           const int qb = uq % A2_NQ; const uint32_t qph = (uq / A2_NQ) & 1;
-          ptx::mbar_wait(&q_empty[qb], qph ^ 1);
+          ptx::mbar_wait_sleep(&q_empty[qb], qph ^ 1, 64);
           ptx::mbar_arrive_expect_tx(&q_full[qb], BOX);
           tma_load_3d(sQ + qb * BLOCK, &tmQKV, &q_full[qb], 0, row0 + qt * A2_BQ, cq);
           if (qt == 0) {
-            ptx::mbar_wait(&kv_empty[slot], ph ^ 1);
+            ptx::mbar_wait_sleep(&kv_empty[slot], ph ^ 1, 64);
             ptx::mbar_arrive_expect_tx(&k_full[slot], BOX * (n1 > 0 ? 2 : 1));
             tma_load_3d(sK + slot * 2 * BLOCK, &tmQKV, &k_full[slot], 0, row0, ck);
             if (n1 > 0) tma_load_3d(sK + slot * 2 * BLOCK + BLOCK, &tmQKV, &k_full[slot], 0, row0 + 128, ck);
@@ -171,6 +171,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             if (ptx::mbar_try_wait(&t_empty[g], ((uq >> 1) & 1) ^ 1) && ptx::mbar_try_wait(&q_full[qb], (uq / A2_NQ) & 1) &&
                 ptx::mbar_try_wait(&k_full[slot], ph))
               break;
+            __nanosleep(32);  // the polling of this warp takes issue slots from the softmax warps of its scheduler
             if (++spins > (1u << 24)) __trap();
           }
           ptx::tc_fence_after();
@@ -189,7 +190,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             }
           }
           ptx::mma_commit(&s_full[g]);
-          if (!pv_done) { while (!pv_ready()) { if (++spins > (1u << 24)) __trap(); } issue_pv(); }
+          if (!pv_done) { while (!pv_ready()) { __nanosleep(32); if (++spins > (1u << 24)) __trap(); } issue_pv(); }
           have_prev = true; p_g = g; p_slot = slot; p_nk16 = nk16; p_u = uq; p_ph = ph; p_last = qt == nlive - 1;
         }
         ++ic;
@@ -275,16 +276,26 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           ptx::tmem_ld_wait();
           const uint32_t w = vw[half * 4 + c];
           uint32_t pk[16];
+          // two whole-chunk code paths behind ONE warp-uniform branch: a per-element `if (w != ~0)` was if-converted into a select plus
+          // two integer ops per element on the unmasked path too (FSEL / LOP3 / ISETP each as frequent as the exp2 in the profile)
+          if (w == 0xffffffffu) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float p0 = ex2f(fmaf(__uint_as_float(s[2 * i]), sl2, -msc));
-            float p1 = ex2f(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -msc));
-            if (w != 0xffffffffu) {
+            for (int i = 0; i < 16; ++i) {
+              const float p0 = ex2f(fmaf(__uint_as_float(s[2 * i]), sl2, -msc));
+              const float p1 = ex2f(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -msc));
+              sum += p0 + p1;
+              pk[i] = pack_bf16x2(p0, p1);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              float p0 = ex2f(fmaf(__uint_as_float(s[2 * i]), sl2, -msc));
+              float p1 = ex2f(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -msc));
               p0 = (w >> (2 * i)) & 1u ? p0 : 0.f;
               p1 = (w >> (2 * i + 1)) & 1u ? p1 : 0.f;
+              sum += p0 + p1;
+              pk[i] = pack_bf16x2(p0, p1);
             }
-            sum += p0 + p1;
-            pk[i] = pack_bf16x2(p0, p1);
           }
           tmem_st16(lane_base + (half ? 192 : 0) + c * 16, pk);
         }
