@@ -168,7 +168,10 @@ __global__ void __launch_bounds__(256, 2) ln_modulate_kernel(const InT* __restri
   extern __shared__ __align__(16) float4 ln_mod4[];
   float4* sc4 = ln_mod4;
   float4* sh4 = ln_mod4 + NV * 64;
-  const int sample = blockIdx.x / blocks_per_sample, blk = blockIdx.x - sample * blocks_per_sample;
+  // rows are walked from the END of the tensor: the GEMM that produced x wrote its last rows most recently (still in L2), and the GEMM
+  // that consumes `out` starts at row 0, which this order writes last
+  const int bid = gridDim.x - 1 - blockIdx.x;
+  const int sample = bid / blocks_per_sample, blk = bid - sample * blocks_per_sample;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nvec = D >> 3;
   const size_t mrow = (size_t)sample * ld_mod;
