@@ -33,6 +33,10 @@ void set_last_error(const char* fmt, ...);
     }                                                                                      \
   } while (0)
 
+// SMs the persistent kernels (GEMM, attention) may occupy: all of them, or fewer while a collective runs beside the backward pass
+// (fitb200_set_sm_limit): NCCL's copy / reduce CTAs need SMs of their own, and a persistent grid that does not fit in one wave next
+// to them runs its last CTAs as a second wave (measured: 8 ms of a 42 ms XL/2 step at 2 GPUs).
+int& sm_limit_ref();
 inline int sm_count() {
   static int n = 0;
   if (n == 0) {
@@ -41,7 +45,8 @@ inline int sm_count() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     if (n <= 0) n = 148;
   }
-  return n;
+  const int lim = sm_limit_ref();
+  return lim > 0 && lim < n ? lim : n;
 }
 
 template <typename T>

@@ -9,6 +9,10 @@
 namespace fitb200 {
 
 static thread_local char g_err[512] = "";
+int& sm_limit_ref() {
+  static int lim = 0;
+  return lim;
+}
 void set_last_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -531,6 +535,12 @@ extern "C" {
 
 const char* fitb200_last_error(void) { return g_err; }
 int fitb200_version(void) { return 100; }
+
+int fitb200_set_sm_limit(int n) {
+  FITB200_CHECK_ARG(n >= 0, "set_sm_limit: n must be >= 0 (0 = every SM)");
+  sm_limit_ref() = n & ~1;  // even: the GEMM schedules CTA pairs
+  return FITB200_OK;
+}
 
 int fitb200_device_ok(void) {
   int dev = 0, major = 0;

@@ -205,12 +205,34 @@ class FiTTrainEngine:
         a = dict(dtype=act, device=dev)
         grads: Dict[str, Tensor] = {}
 
-        def emit(tag, names):
+        def emit(tag, names, flat=None):
             if on_grads is not None:
-                on_grads(tag, {n: grads[n] for n in names})
+                if flat is not None:
+                    on_grads(tag, {n: grads[n] for n in names}, flat)
+                else:
+                    on_grads(tag, {n: grads[n] for n in names})
 
-        def wgrad(dy: Tensor, x: Tensor) -> Tensor:           # dW[N, K] = dy[M, N]^T x[M, K]
-            return ops.gemm(dy, x, None, torch.empty(dy.shape[1], x.shape[1], **f32), EPI_BIAS, a_mn=True, b_mn=True)
+        def wgrad(dy: Tensor, x: Tensor, out: Optional[Tensor] = None) -> Tensor:           # dW[N, K] = dy[M, N]^T x[M, K]
+            return ops.gemm(dy, x, None, torch.empty(dy.shape[1], x.shape[1], **f32) if out is None else out, EPI_BIAS, a_mn=True, b_mn=True)
+
+        def bucket(shapes):
+            """One flat zeroed fp32 buffer holding the listed gradients back to back (16-byte aligned offsets): the data-parallel
+            all-reduce runs on it in place -- no packing copy before and no scatter copy after the collective."""
+            offs, n = [], 0
+            for shp in shapes:
+                offs.append(n)
+                cnt = 1
+                for v in shp:
+                    cnt *= v
+                n += (cnt + 3) // 4 * 4
+            flat = torch.zeros(n, **f32)
+            views = []
+            for off, shp in zip(offs, shapes):
+                cnt = 1
+                for v in shp:
+                    cnt *= v
+                views.append(flat[off:off + cnt].view(*shp))
+            return flat, views
 
         def dgrad(dy: Tensor, w: Tensor, out_dtype=None) -> Tensor:  # dx[M, K] = dy[M, N] w[N, K]
             return ops.gemm(dy, w, None, torch.empty(dy.shape[0], w.shape[1], dtype=out_dtype or act, device=dev), EPI_BIAS, b_mn=True)
@@ -238,37 +260,47 @@ class FiTTrainEngine:
             pre = f"blocks.{i}."
             mv = [S.mod[:, (6 * i + k) * D:(6 * i + k + 1) * D] for k in range(6)]
             dv = [dmod[:, (6 * i + k) * D:(6 * i + k + 1) * D] for k in range(6)]
+            flat, (g_fc2b, g_fc2w, g_f1gw, g_f1xw, g_f1gb, g_f1xb, g_pb, g_pw, g_qb, g_qw, g_aw, g_ab) = bucket(
+                [(D,), (D, H), (H, D), (H, D), (H,), (H,), (D,), (D, D), (3 * D,), (3 * D, D), (6 * D, D), (6 * D,)])
             # x_out = x_mid + gate_mlp * fc2(g)
-            db = torch.zeros(D, **f32)
-            dy2 = ops.gate_bwd(dx, b.y2, mv[5], nm, R, T, torch.empty(M, D, **a), dv[5], nm, db)
-            grads[pre + "ffn.fc2.bias"] = db
-            dw2 = wgrad(dy2, b.g)
-            grads[pre + "ffn.fc2.weight"] = dw2[:, :H].contiguous() if Hp != H else dw2
+            dy2 = ops.gate_bwd(dx, b.y2, mv[5], nm, R, T, torch.empty(M, D, **a), dv[5], nm, g_fc2b)
+            grads[pre + "ffn.fc2.bias"] = g_fc2b
+            if Hp != H:
+                g_fc2w.copy_(wgrad(dy2, b.g)[:, :H])
+            else:
+                wgrad(dy2, b.g, g_fc2w)
+            grads[pre + "ffn.fc2.weight"] = g_fc2w
             dg = dgrad(dy2, e["fc2_w"])
             # g = silu(u_gate) * u_up
             db1 = torch.zeros(2 * Hp, **f32)
             du = ops.swiglu_bwd(dg, b.u, torch.empty(M, 2 * Hp, **a), db1)
             dw1 = wgrad(du, b.h2).view(Hp // 16, 2, 16, D)
-            grads[pre + "ffn.fc1_g.weight"] = dw1[:, 0].reshape(Hp, D)[:H].contiguous()
-            grads[pre + "ffn.fc1_x.weight"] = dw1[:, 1].reshape(Hp, D)[:H].contiguous()
+            g_f1gw.copy_(dw1[:, 0].reshape(Hp, D)[:H]); g_f1xw.copy_(dw1[:, 1].reshape(Hp, D)[:H])   # un-interleave the packed fc1 rows
+            grads[pre + "ffn.fc1_g.weight"], grads[pre + "ffn.fc1_x.weight"] = g_f1gw, g_f1xw
             db1 = db1.view(Hp // 16, 2, 16)
-            grads[pre + "ffn.fc1_g.bias"] = db1[:, 0].reshape(Hp)[:H].contiguous()
-            grads[pre + "ffn.fc1_x.bias"] = db1[:, 1].reshape(Hp)[:H].contiguous()
+            g_f1gb.copy_(db1[:, 0].reshape(Hp)[:H]); g_f1xb.copy_(db1[:, 1].reshape(Hp)[:H])
+            grads[pre + "ffn.fc1_g.bias"], grads[pre + "ffn.fc1_x.bias"] = g_f1gb, g_f1xb
             dh2 = dgrad(du, e["fc1_w"])
             dx_mid = ops.ln_modulate_bwd(dh2, b.x_mid, b.mean2, b.rstd2, mv[4], nm, T, dx, torch.empty(M, D, **a), dv[3], dv[4], nm)
             # x_mid = x_in + gate_msa * proj(att)
-            dbp = torch.zeros(D, **f32)
-            dy1 = ops.gate_bwd(dx_mid, b.y1, mv[2], nm, R, T, torch.empty(M, D, **a), dv[2], nm, dbp)
-            grads[pre + "attn.proj.bias"] = dbp
-            grads[pre + "attn.proj.weight"] = wgrad(dy1, b.att)
+            dy1 = ops.gate_bwd(dx_mid, b.y1, mv[2], nm, R, T, torch.empty(M, D, **a), dv[2], nm, g_pb)
+            grads[pre + "attn.proj.bias"] = g_pb
+            grads[pre + "attn.proj.weight"] = wgrad(dy1, b.att, g_pw)
             datt = dgrad(dy1, e["proj_w"])
             dqkv = ops.attention_bwd(b.qkv, S.pos, S.kv_len, S.mask, R, T, h, d, b.att, datt, b.lse, torch.empty(M, 3 * D, **a), prerotated=bf16)
-            grads[pre + "attn.qkv.bias"] = ops.colsum(dqkv, torch.zeros(3 * D, **f32))
-            grads[pre + "attn.qkv.weight"] = wgrad(dqkv, b.h1)
+            grads[pre + "attn.qkv.bias"] = ops.colsum(dqkv, g_qb)
+            grads[pre + "attn.qkv.weight"] = wgrad(dqkv, b.h1, g_qw)
             dh1 = dgrad(dqkv, e["qkv_w"])
             dx = ops.ln_modulate_bwd(dh1, b.x_in, b.mean1, b.rstd1, mv[1], nm, T, dx_mid, torch.empty(M, D, **a), dv[0], dv[1], nm)
+            # adaLN table of this block: mod_i = silu(c) W_i^T + b_i (fit.py:323-324,329).  Its six dmod chunks are final now, so the
+            # gradient (a third of all parameters) joins this block's bucket instead of waiting for the end of the backward
+            dmod_i = dmod[:, 6 * i * D:6 * (i + 1) * D]
+            dmod_ia = dmod_i.contiguous() if act == torch.float32 else ops.cast(dmod_i.contiguous(), torch.empty(R, 6 * D, **a))
+            grads[pre + "adaLN_modulation.1.weight"] = wgrad(dmod_ia, S.silu_c, g_aw)
+            grads[pre + "adaLN_modulation.1.bias"] = ops.colsum(dmod_i, g_ab)
             emit(pre[:-1], [pre + s for s in ("ffn.fc2.bias", "ffn.fc2.weight", "ffn.fc1_g.weight", "ffn.fc1_x.weight", "ffn.fc1_g.bias",
-                                              "ffn.fc1_x.bias", "attn.proj.bias", "attn.proj.weight", "attn.qkv.bias", "attn.qkv.weight")])
+                                              "ffn.fc1_x.bias", "attn.proj.bias", "attn.proj.weight", "attn.qkv.bias", "attn.qkv.weight",
+                                              "adaLN_modulation.1.weight", "adaLN_modulation.1.bias")], flat)
             S.blocks[i] = None  # free this block's activations
 
         # ---- x_embedder (fit.py:387-388,499-501): no gradient with respect to the latents is needed
@@ -278,13 +310,10 @@ class FiTTrainEngine:
 
         # ---- adaLN tables of all blocks + final layer: mod = silu(c) W_ada^T + b  (fit.py:323-324,329; dit.py:134-139)
         dmod_a = dmod if act == torch.float32 else ops.cast(dmod, torch.empty(R, nm, **a))
-        dW_ada = wgrad(dmod_a, S.silu_c)
-        db_ada = ops.colsum(dmod, torch.zeros(nm, **f32))
-        for i in range(L):
-            grads[f"blocks.{i}.adaLN_modulation.1.weight"] = dW_ada[6 * i * D:6 * (i + 1) * D]
-            grads[f"blocks.{i}.adaLN_modulation.1.bias"] = db_ada[6 * i * D:6 * (i + 1) * D]
-        grads["final_layer.adaLN_modulation.1.weight"] = dW_ada[6 * L * D:]
-        grads["final_layer.adaLN_modulation.1.bias"] = db_ada[6 * L * D:]
+        dmod_f = dmod[:, 6 * L * D:].contiguous()
+        dmod_fa = dmod_f if act == torch.float32 else ops.cast(dmod_f, torch.empty(R, 2 * D, **a))
+        grads["final_layer.adaLN_modulation.1.weight"] = wgrad(dmod_fa, S.silu_c)
+        grads["final_layer.adaLN_modulation.1.bias"] = ops.colsum(dmod_f, torch.zeros(2 * D, **f32))
         dsilu_c = dgrad(dmod_a, W.ada_w, torch.float32)
         dc = ops.silu_bwd(dsilu_c, S.c, torch.empty(R, D, **f32))
         # ---- c = t_emb + y_emb (fit.py:505): label table scatter, t-embedder MLP (fit.py:55-57,84-85)
@@ -295,5 +324,5 @@ class FiTTrainEngine:
         dpre = ops.silu_bwd(dt1, S.t_pre, torch.empty(R, D, **f32))
         grads["t_embedder.mlp.0.bias"] = ops.colsum(dpre, torch.zeros(D, **f32))
         grads["t_embedder.mlp.0.weight"] = wgrad(dpre, S.tfreq)
-        emit("embedders", [n for n in grads if not n.startswith("blocks.") or "adaLN" in n])
+        emit("embedders", [n for n in grads if not n.startswith("blocks.") and not n.startswith("final_layer.linear")])
         return grads

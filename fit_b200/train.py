@@ -5,6 +5,8 @@ from __future__ import annotations
 
 from typing import Dict, List, Optional
 
+import os
+
 import torch
 
 from . import ops
@@ -101,6 +103,13 @@ class GradSync:
         self.enabled = True
         self._pending: List = []
         self._stream = None
+        # NCCL's CTAs need SMs of their own next to the persistent GEMM / attention grids: leave `reserve_sms` free while syncing.
+        # (Set NCCL_MAX_CTAS <= reserve_sms before the process group is created to hold NCCL to that budget.)
+        self.reserve_sms = int(os.environ.get("FITB200_DDP_RESERVE_SMS", "8")) if self.world > 1 and self.avg_in_collective else 0
+        if self.reserve_sms > 0:
+            from . import _lib as L
+            n = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+            L.check(L.lib().fitb200_set_sm_limit(n - self.reserve_sms), "set_sm_limit")
 
     def attach(self, model):
         object.__setattr__(model, "_grad_sync", self)
@@ -114,11 +123,15 @@ class GradSync:
     def no_sync(self):
         return GradSync._NoSync(self)
 
-    def on_grads(self, tag: str, grads: Dict[str, Tensor]):
+    def on_grads(self, tag: str, grads: Dict[str, Tensor], flat: Optional[Tensor] = None):
+        """``flat``: the gradients are views into this one buffer (the training engine allocates each block's gradients that way):
+        it is all-reduced in place, with no packing copy before and no scatter copy after."""
         if not self.enabled or self.world == 1:
             return
         tensors = list(grads.values())
-        flat = torch.cat([g.reshape(-1) for g in tensors])   # packing copy (no arithmetic)
+        in_place = flat is not None
+        if not in_place:
+            flat = torch.cat([g.reshape(-1) for g in tensors])   # packing copy (no arithmetic)
         if flat.is_cuda:
             if self._stream is None:
                 self._stream = torch.cuda.Stream(device=flat.device)
@@ -130,7 +143,7 @@ class GradSync:
             flat.record_stream(self._stream)
         else:
             work = self.dist.all_reduce(flat, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True)
-        self._pending.append((flat, tensors, work))
+        self._pending.append((flat, [] if in_place else tensors, work))
 
     def finish(self):
         if not self._pending:

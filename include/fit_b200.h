@@ -239,6 +239,10 @@ int fitb200_masked_mse_bwd(const float* out, const float* target, const uint8_t*
                            const float* gscale, void* dout, int dout_dtype, fitb200_stream_t stream);
 
 
+/* Cap on the SMs the persistent kernels (GEMM, attention) occupy; 0 = all.  fit_b200.train.GradSync lowers it while NCCL's all-reduce
+ * CTAs run beside the backward pass (DDP, FiT/train.py:287-288 via Lightning) so that both fit in one wave.  Process-wide, host-side. */
+int fitb200_set_sm_limit(int n);
+
 /* ---- masked_FiT token sub-sampling: ImageNetLatentIterator.subsample / collate
  * (masked_FiT/preprocess/iterators.py:142-169) for a whole batch in one launch.  Sample s holds n_tokens[s] valid tokens in
  * latent[s, :, :P], pos[s, :, :d] (d = RoPE row width) and mask[s, :] (bytes).  With T' = Tout:
