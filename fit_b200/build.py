@@ -24,6 +24,8 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr", "-DFITB200_BUILD",
 ]
+if os.environ.get("FITB200_TUNING") == "1":   # measurement-only switches (e.g. FITB200_GEMM_DBG: GEMM mainloop ceiling); never in the product build
+    NVCC_FLAGS.append("-DFITB200_TUNING")
 
 
 def _nvcc() -> str:

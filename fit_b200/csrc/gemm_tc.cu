@@ -50,6 +50,7 @@ struct GtParams {
   const float* bias;
   const float* gate; long ld_gate; int rows_per_sample;
   const float* rope_freqs; int rope_rows, rope_tokens, rope_hd, rope_cols;
+  int tail_rows;  // K-major B: rows of the narrower TMA box (tmBt) used for the last, cut column tile (0 = always the full box)
   int dbg;  // FITB200_GEMM_DBG=1: epilogue releases the accumulator without reading it (mainloop ceiling measurement only)
 };
 
@@ -66,7 +67,8 @@ __device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
 template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false>
 __global__ void __launch_bounds__(GT_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GtParams p) {
+               const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmBt,
+               const GtParams p) {
   using Cfg = GtCfg<BN, EPI, PAIR>;
   static_assert(!PAIR || !BMN || Cfg::BNL % 64 == 0, "pair tiles with a contraction-major B: whole 64-column boxes per CTA");
   constexpr int STAGES = Cfg::STAGES;
@@ -111,6 +113,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ptx::prefetch_tmap(&tmB);
     ptx::prefetch_tmap(&tmOut);
     if (RESID) ptx::prefetch_tmap(&tmRes);
+    if (p.tail_rows > 0) ptx::prefetch_tmap(&tmBt);
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
@@ -141,7 +144,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           if (PAIR) {
             // both CTAs' bytes are counted on the LEADER's full barrier (the only one the MMA thread waits on)
-            if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+            // the cut last column tile fetches only the B rows its MMAs read: a full box would make that tile as expensive as a whole one
+            const bool tail = !BMN && nn < BN && p.tail_rows > 0;
+            const uint32_t stage_bytes = tail ? Cfg::A_BYTES + p.tail_rows * 128 : Cfg::STAGE_BYTES;
+            if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * stage_bytes);
             const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
             if (AMN) {
 #pragma unroll
@@ -153,12 +159,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
               for (int b = 0; b < Cfg::BNL / 64; ++b) ptx::tma_load_2d_pair(smemB + stage * Cfg::B_BYTES + b * 8192, &tmB, fb, n0 + b * 64, kb * GT_BK);
             } else {
-              ptx::tma_load_2d_pair(smemB + stage * Cfg::B_BYTES, &tmB, fb, kb * GT_BK, n0);
+              ptx::tma_load_2d_pair(smemB + stage * Cfg::B_BYTES, tail ? &tmBt : &tmB, fb, kb * GT_BK, n0);
             }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
             continue;
           }
-          ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+          const bool tail1 = !BMN && nn < BN && p.tail_rows > 0;
+          ptx::mbar_arrive_expect_tx(&full_bar[stage], tail1 ? Cfg::A_BYTES + p.tail_rows * 128 : Cfg::STAGE_BYTES);
           if (AMN) {
 #pragma unroll
             for (int b = 0; b < GT_BM / 64; ++b) ptx::tma_load_2d(smemA + stage * Cfg::A_BYTES + b * 8192, &tmA, &full_bar[stage], m0 + b * 64, kb * GT_BK);
@@ -169,7 +176,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int b = 0; b < BN / 64; ++b) ptx::tma_load_2d(smemB + stage * Cfg::B_BYTES + b * 8192, &tmB, &full_bar[stage], n0 + b * 64, kb * GT_BK);
           } else {
-            ptx::tma_load_2d(smemB + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * GT_BK, n0);
+            ptx::tma_load_2d(smemB + stage * Cfg::B_BYTES, tail1 ? &tmBt : &tmB, &full_bar[stage], kb * GT_BK, n0);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -272,12 +279,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+#ifdef FITB200_TUNING  // measurement-only builds (FITB200_TUNING=1 python -m fit_b200.build): mainloop ceiling with the epilogue skipped
       if (p.dbg) {
         ptx::tc_fence_before();
         if (PAIR) { __syncwarp(); if (lane == 0) ptx::mbar_arrive_cluster_relaxed(tempty_leader + as * 8); } else ptx::mbar_arrive(&tempty_bar[as]);
         q += NSLAB;
         continue;
       }
+#endif
 #pragma unroll 1
       for (int slab = 0; slab < NSLAB; ++slab, ++q) {
         const int buf = q & 1;
@@ -447,7 +456,7 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int dtype, long rows, long
 template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false>
 static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   using Cfg = GtCfg<BN, EPI, PAIR>;
-  CUtensorMap tmA, tmB, tmOut, tmRes;
+  CUtensorMap tmA, tmB, tmOut, tmRes, tmBt;
   int rc = AMN ? make_tmap(&tmA, a.A, FITB200_BF16, a.K, a.M, a.lda, GT_BK, 64) : make_tmap(&tmA, a.A, FITB200_BF16, a.M, a.K, a.lda, GT_BM, GT_BK);
   if (rc) return rc;
   rc = BMN ? make_tmap(&tmB, a.B, FITB200_BF16, a.K, a.N, a.ldb, GT_BK, 64) : make_tmap(&tmB, a.B, FITB200_BF16, a.N, a.K, a.ldb, Cfg::BNL, GT_BK);
@@ -457,6 +466,18 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   rc = make_tmap(&tmOut, a.out, a.out_dtype, a.M, n_out, a.ldo, 32, outc);  // one store per lane quarter: 32 rows
   if (rc) return rc;
   tmRes = tmOut;
+  tmBt = tmB;
+  int tail_rows = 0;
+  if (!BMN && a.N % BN != 0 && a.N > BN) {  // the cut last column tile: a box of just the rows each CTA's MMAs read
+    const int gran = PAIR ? 32 : 16, nn = (a.N % BN + gran - 1) / gran * gran;
+    tail_rows = PAIR ? nn / 2 : nn;
+    if (tail_rows < Cfg::BNL) {
+      rc = make_tmap(&tmBt, a.B, FITB200_BF16, a.N, a.K, a.ldb, tail_rows, GT_BK);
+      if (rc) return rc;
+    } else {
+      tail_rows = 0;
+    }
+  }
   if (EPI == FITB200_EPI_BIAS_GATE_RESID) {
     rc = make_tmap(&tmRes, a.resid, a.out_dtype, a.M, a.N, a.ld_resid, 32, outc);
     if (rc) return rc;
@@ -465,8 +486,13 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   p.M = a.M; p.N = a.N; p.K = a.K; p.bias = a.bias;
   p.gate = a.gate; p.ld_gate = a.ld_gate; p.rows_per_sample = a.rows_per_sample;
   p.rope_freqs = a.rope_freqs; p.rope_rows = a.rope_rows; p.rope_tokens = a.rope_tokens; p.rope_hd = a.rope_head_dim; p.rope_cols = a.rope_cols;
+#ifdef FITB200_TUNING
   static const int dbg = [] { const char* e = getenv("FITB200_GEMM_DBG"); return e ? atoi(e) : 0; }();
   p.dbg = dbg;
+#else
+  p.dbg = 0;
+#endif
+  p.tail_rows = tail_rows;
   auto kern = gemm_tc_kernel<BN, EPI, OutT, AMN, BMN, PAIR>;
   static bool attr_done = false;  // per template instantiation
   if (!attr_done) {
@@ -483,13 +509,13 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmOut, tmRes, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmOut, tmRes, tmBt, p);
     if (e != cudaSuccess) { set_last_error("gemm_bf16_tc: pair launch failed: %s", cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
     return FITB200_OK;
   }
   const int tiles = ceil_div(a.M, GT_BM) * ceil_div(a.N, BN);
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  kern<<<grid, GT_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmOut, tmRes, p);
+  kern<<<grid, GT_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmOut, tmRes, tmBt, p);
   FITB200_CHECK_LAUNCH("gemm_bf16_tc");
   return FITB200_OK;
 }
