@@ -194,3 +194,39 @@ def test_sampling_driver_batches_and_shards():
     assert torch.equal(torch.cat(order), full)
     wide, _ = run(1, 0, (64, 128))        # 8 x 16 latent = 32 tokens
     assert wide.shape == (7, 4, 8, 16) and bool(torch.isfinite(wide).all())
+
+
+def test_headline_size_properties():
+    """BASELINE config 3 at full size (FiT-XL/2, 256 images = 512 rows x 256 tokens) through size-independent properties:
+    two denoising steps of the whole batch == the same steps on its two halves (no cross-sample coupling anywhere on the path: CTA-pair
+    GEMM tiles, persistent attention, CFG step; noise keyed by the global image index), bit for bit, and everything stays finite."""
+    import bench
+    from fit_b200.diffusion import create_diffusion
+    from fit_b200.models.fit import FiT_models
+    from fit_b200.rope import precompute_freqs_cis_2d
+    from fit_b200.sampler import CFGSampler
+    torch.manual_seed(0)
+    with torch.device("cuda"):
+        model = FiT_models["FiT-XL/2"](precision="bf16")
+    bench.randomize_zero_init(model)
+    model.eval()
+    d = create_diffusion("250")
+    g = torch.Generator().manual_seed(5)
+    B = 256
+    z = torch.randn(B, 4, 32, 32, generator=g)
+    y = torch.randint(0, 1000, (B,), generator=g)
+    pos = torch.tensor(precompute_freqs_cis_2d(72, 16, 16, max_length=256), dtype=torch.float32)[None]
+    s = CFGSampler(model, d, batch=B, latent_hw=(32, 32), cfg_scale=1.5, seed=9)
+    s.load(z, y, pos); s.run(2)
+    full = s.x.clone()
+    assert bool(torch.isfinite(full).all())
+    del s
+    parts = []
+    for k in range(2):
+        sk = CFGSampler(model, d, batch=B // 2, latent_hw=(32, 32), cfg_scale=1.5, seed=9, row_offset=k * (B // 2))
+        sk.load(z[k * 128:(k + 1) * 128], y[k * 128:(k + 1) * 128], pos); sk.run(2)
+        parts.append(sk.x.clone())
+        del sk
+    assert torch.equal(torch.cat(parts), full)
+    # the update actually moved the latents (a dead kernel would also be "shard invariant")
+    assert float((full.cpu() - z).abs().mean()) > 1e-3
