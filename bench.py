@@ -152,7 +152,7 @@ def randomize_zero_init(model, seed=1):
             p.data.copy_(torch.randn(p.shape, generator=g) * 0.02)
 
 
-def ncu_traffic(tag="r1e"):
+def ncu_traffic(tag="r1f"):
     """DRAM bytes (read + write) per launch of the block kernels from the committed `ncu --set full` capture of tools/prof_kernels.py at
     the same shape (profiles/<tag>_ncu_full_block_kernels.csv); {} when the summary is absent."""
     import csv
@@ -244,7 +244,7 @@ def kernel_rooflines(model, sampler, peaks, iters=10):
     for k, b in ncu_traffic().items():
         if k in res:
             res[k]["traffic"] = b
-            res[k]["traffic_source"] = "profiles/r1e_ncu_full_block_kernels.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+            res[k]["traffic_source"] = "profiles/r1f_ncu_full_block_kernels.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
     return res
 
 
