@@ -276,3 +276,28 @@ def test_attention(ops, dt, T, h, d, lens, nonprefix):
         out1 = torch.empty(R * T, h * d, dtype=dt, device="cuda")
         ops.attention(qkv.to(dt).cuda().view(R * T, 3 * h * d), freqs[:1].contiguous().cuda(), kv, None, R, T, h, d, out1)
         assert rel_l2(out1.float().cpu().view(R, T, h * d), want) < tol
+
+
+@pytest.mark.parametrize("h,d", [(16, 72), (12, 64)])
+def test_attention_persistent_many_items(ops, h, d):
+    """attn_tc2 (persistent: several (sample, head) items per CTA): ring-buffer reuse, alternating softmax groups and skipped items with
+    ragged key counts -- 0 (item skipped), <= 128 (one query unit) and > 128 (two units) mixed so that unit parity and ring slots drift."""
+    T, R = 256, 40
+    g = torch.Generator().manual_seed(17)
+    lens = [256, 0, 1, 128, 129, 200, 16, 0, 255, 64] + [int(x) for x in torch.randint(0, 257, (R - 10,), generator=g)]
+    qkv, freqs, mask = _attn_case(R, T, h, d, lens, seed=3, nonprefix=False)
+    q3, k3, v3 = qkv.bfloat16().float().permute(2, 0, 3, 1, 4)
+    qr, kr = fo.rope_rotate(q3, freqs).bfloat16().float(), fo.rope_rotate(k3, freqs).bfloat16().float()
+    want = fo.attention_core(qr, kr, v3, mask).transpose(1, 2).reshape(R, T, -1)
+    qkv_rot = torch.stack([qr, kr, v3], 0).permute(1, 3, 0, 2, 4).contiguous().bfloat16()
+    kv, _ = ops.mask_to_kvlen(mask.cuda())
+    out = torch.full((R * T, h * d), float("nan"), dtype=torch.bfloat16, device="cuda")
+    lse = torch.full((R, h, T), float("nan"), device="cuda")
+    ops.attention(qkv_rot.cuda().view(R * T, 3 * h * d), None, kv, mask.cuda(), R, T, h, d, out, lse, prerotated=True)
+    assert bool(torch.isfinite(out.float()).all()) and bool(torch.isfinite(lse).all())   # every row written, padded ones included
+    out = out.float().cpu().view(R, T, h * d)
+    for r, L in enumerate(lens):
+        if L > 0:
+            assert rel_l2(out[r, :L], want[r, :L]) < 5e-3, (r, L)
+        q0 = (L + 127) // 128 * 128
+        assert float(out[r, q0:].abs().max()) == 0.0 if q0 < T else True   # query tiles beyond kv_len are zero rows
