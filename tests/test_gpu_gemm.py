@@ -45,7 +45,9 @@ def test_gemm_bias_and_silu(ops, wdt, odt, M, N, K):
 
 @pytest.mark.parametrize("wdt,adt", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16), (torch.bfloat16, torch.float32)])
 @pytest.mark.parametrize("M,N,K,rps", [(512, 1152, 1152, 256), (400, 768, 2048, 200), (128, 128, 64, 64), (96, 144, 384, 32),
-                                       (1024, 1152, 3072, 256)])
+                                       (1024, 1152, 3072, 256),
+                                       (16640, 1152, 128, 256),     # 325 tiles: several per CTA pair (TMEM stage / ring phases wrap), cut last column tile
+                                       (13200, 864, 192, 200)])     # ragged last row block, tiles straddle samples
 def test_gemm_gate_residual(ops, wdt, adt, M, N, K, rps):
     A, B, bias = _inputs(M, N, K, M + N, wdt)
     g = torch.Generator().manual_seed(1)
@@ -62,7 +64,7 @@ def test_gemm_gate_residual(ops, wdt, adt, M, N, K, rps):
     assert rel_l2(xs.float(), want) < (1e-5 if adt == torch.float32 else 4e-3)
 
 
-@pytest.mark.parametrize("M,K,H", [(256, 1152, 3072), (200, 768, 2048), (130, 128, 341), (64, 1024, 2730)])
+@pytest.mark.parametrize("M,K,H", [(256, 1152, 3072), (200, 768, 2048), (130, 128, 341), (64, 1024, 2730), (16484, 128, 1024)])
 def test_gemm_swiglu_fp32(ops, M, K, H):
     g = torch.Generator().manual_seed(H)
     A = torch.randn(M, K, generator=g)
@@ -76,7 +78,7 @@ def test_gemm_swiglu_fp32(ops, M, K, H):
     assert float(out[:, H:].abs().sum()) == 0.0
 
 
-@pytest.mark.parametrize("M,K,H", [(256, 1152, 3072), (200, 768, 2048), (130, 128, 341), (64, 1024, 2730)])
+@pytest.mark.parametrize("M,K,H", [(256, 1152, 3072), (200, 768, 2048), (130, 128, 341), (64, 1024, 2730), (16484, 128, 1024)])
 def test_gemm_swiglu_bf16_packed(ops, M, K, H):
     """Packed [2*Hp, K] weight: 16 rows of fc1_g then the matching 16 rows of fc1_x (the engine's layout)."""
     g = torch.Generator().manual_seed(H + 1)
@@ -127,7 +129,8 @@ def test_gemm_argument_errors(ops):
 
 
 @pytest.mark.parametrize("odt", [torch.bfloat16, torch.float32])
-@pytest.mark.parametrize("R,T,h,d,rows", [(2, 256, 16, 72, 1), (3, 200, 12, 64, 3), (2, 64, 2, 72, 2), (4, 33, 2, 64, 1)])
+@pytest.mark.parametrize("R,T,h,d,rows", [(2, 256, 16, 72, 1), (3, 200, 12, 64, 3), (2, 64, 2, 72, 2), (4, 33, 2, 64, 1),
+                                          (70, 256, 4, 72, 1), (66, 200, 2, 64, 66)])   # many tiles per CTA pair; smem RoPE rows reloaded per row block
 def test_gemm_qkv_rope_epilogue(ops, odt, R, T, h, d, rows):
     """EPI_BIAS_ROPE: qkv Linear (fit.py:234) + apply_rotary_emb on the q and k columns (fit.py:160-174), v untouched."""
     from oracle import fit_oracle as fo
