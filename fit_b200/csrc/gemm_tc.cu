@@ -294,13 +294,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int nout = SWIGLU ? (nacc >> 1) : nacc;  // first output column
         uint8_t* obuf = smemOut + buf * GT_SLAB_BYTES + row * 128;
         const uint8_t* rbuf = smemRes + buf * GT_SLAB_BYTES + row * 128;
+        const bool live = nacc < p.N;  // tile-uniform: slabs beyond N are skipped (their store would be fully clipped)
+        constexpr int HACC = ACCC / 2;  // accumulator columns of this warp's half slab
+        // the accumulator columns are requested BEFORE the staging-buffer waits and the quarter barrier: the TMEM round trip overlaps them
+        uint32_t accr[HACC];
+        if (live) {
+#pragma unroll
+          for (int c = 0; c < HACC / 16; ++c) ptx::tmem_ld16(taddr + slab * ACCC + half * HACC + c * 16, *reinterpret_cast<uint32_t(*)[16]>(accr + c * 16));
+        }
         // the TMA store that read this staging buffer two slabs ago must have finished reading it
         if (leader) ptx::tma_store_wait_read<1>();
         if (RESID) ptx::mbar_wait(&res_bar[quarter * 2 + buf], (q >> 1) & 1);
         ptx::named_bar_sync(qbar, 64);
-        const bool live = nacc < p.N;  // tile-uniform: slabs beyond N are skipped (their store would be fully clipped)
         if (live) {
-          constexpr int HACC = ACCC / 2;  // accumulator columns of this warp's half slab
           float acc[HACC];
           // RoPE table of this thread's 4 chunks, issued ahead of the TMEM loads (L2 latency hidden behind them)
           float4 fq[ROPE ? 4 : 1][CW / 4];
@@ -316,9 +322,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               if (hcol >= p.rope_hd) hcol -= p.rope_hd;
             }
           }
-#pragma unroll
-          for (int c = 0; c < HACC / 16; ++c) tmem_ld16f(taddr + slab * ACCC + half * HACC + c * 16, acc + c * 16);
           ptx::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < HACC; ++i) acc[i] = __uint_as_float(accr[i]);
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {  // this warp's 4 of the 8 x 16-byte chunks per 128-byte row
             const int j = half * 4 + jj;
