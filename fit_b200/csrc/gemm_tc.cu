@@ -195,7 +195,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (PAIR) ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1); else ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        // N = 192 issues at the rate of N = 256 on B200 (measured): tiles are 256 (or 128) wide and only the last one is cut to what is left
+        // tiles are 256 wide and only the last one of a row is cut to what is left (192- and 128-wide tiles measured 0.73x / 0.50x the
+        // throughput of 256-wide ones: the MMA itself runs at full rate for N >= 128 (tools/probe/umma_rate.cu), the operand bytes staged
+        // per flop are what grows)
         const int nn = min(BN, (p.N - (tile % tiles_n) * BN + NGRAN - 1) / NGRAN * NGRAN);
         const uint32_t idesc = idesc0 | ((uint32_t)(nn >> 3) << 17);
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -568,7 +570,7 @@ static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
 
 template <typename OutT>
 static int dispatch_bn(const fitb200_gemm_args& a, cudaStream_t s) {
-  // 256-wide tiles (the last one of a row is cut to the columns that are left); N = 192 MMAs cost as much as N = 256 ones.
+  // 256-wide tiles (the last one of a row is cut to the columns that are left): narrower tiles stage more operand bytes per flop.
   // FITB200_GEMM_BN=128|192|256 overrides (tuning / tests)
   static const int force = [] { const char* e = getenv("FITB200_GEMM_BN"); return e ? atoi(e) : 0; }();
   // (tried: 128-wide tiles when they need fewer wave x width units at training sizes -- 47.4 vs 42.5 ms per XL/2 step: N = 128 tiles are
