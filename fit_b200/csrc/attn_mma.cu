@@ -8,6 +8,7 @@ namespace fitb200 {
 
 int attn_fwd_f32(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask,
                  int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s);
+int attn_fwd_tc3(const void* qkv, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s);
 int attn_fwd_tc(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask,
                 int R, int Tn, int h, int d, int prerotated, void* out, float* lse, cudaStream_t s);
 
@@ -303,6 +304,11 @@ extern "C" int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, 
   if (dtype == FITB200_BF16) {
     // sequences that fit the resident K/V tile (every trained shape): tcgen05 kernel; longer (extrapolation): chunked mma.sync kernel
     if (T <= 256 && (d == 64 || d == 72)) return attn_fwd_tc(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, d, pre, out, lse, s);
+    if (pre && (d == 64 || d == 72) && ((uintptr_t)out & 15) == 0) {
+      // KV-blocked tcgen05 kernel (attn_tc3.cu); FITB200_ATTN_MMA=1 keeps the mma.sync kernel below (A/B timing, debugging)
+      static const bool use_mma = [] { const char* e = getenv("FITB200_ATTN_MMA"); return e && e[0] == '1'; }();
+      if (!use_mma) return attn_fwd_tc3(qkv, kv_len, mask, R, T, h, d, out, lse, s);
+    }
     if (pre) freqs = nullptr;
     if (d == 64) return launch_attn_mma<64>(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, out, lse, s);
     if (d == 72) return launch_attn_mma<72>(qkv, freqs, freqs_rows, kv_len, mask, R, T, h, out, lse, s);

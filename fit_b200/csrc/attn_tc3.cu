@@ -1,0 +1,414 @@
+// KV-blocked bf16 attention forward on tcgen05 / TMEM for sequences LONGER than 256 tokens (resolution extrapolation: BASELINE
+// config 5, 320x320 = 400 tokens ... 1024x1024 = 4096 tokens) whose q and k already carry the RoPE (qkv GEMM epilogue
+// FITB200_EPI_BIAS_ROPE).  Same arithmetic as Attention.forward (fit.py:176-188; head merge fit.py:220-227) with the softmax
+// evaluated block by block over the keys (running row max / row sum, O rescaled when the max moves), the schedule of attn_tc2.cu
+// (persistent CTAs, event-driven MMA issuer, row-per-thread softmax groups) extended by a key loop:
+//   warps 0, 1  TMA producers of group 0 / 1: per 128-query unit Q once, then K_j / V_j blocks of 128 keys through a 2-stage ring
+//   warp 2      MMA issuer for both groups: S_j = Q K_j^T (TMEM region g, columns [0, 128)), then O += P_j V_j (columns [128, 128+DP))
+//   warps 4-7   softmax / epilogue group 0, warps 8-11 group 1: each group owns one unit at a time; one thread = one query row:
+//               pass 1 block max, pass 2 P_j = exp2(S_j - max) as bf16 over the S columns it came from, O row rescaled in TMEM when
+//               the running max moved (skipped per warp when no row's did), at the end O / rowsum -> staging (the unit's Q buffer)
+//               -> one TMA store per warp (rows clipped at the sample's token count by the 3-D map).
+// The two groups interleave on the tensor pipe: while one runs its softmax the other's S / PV multiply.  tcgen05.mma executes in
+// issue order, so S_{j+1} (which overwrites P_j) is simply issued behind P_j V_j; the only waits the issuer has are data (TMA) and
+// p_ready.  Only keys < kv_len are multiplied (N / K of a block = round16 of its live keys); query tiles at or beyond kv_len are
+// skipped (zero rows).
+#include <cstring>
+
+#include "common.cuh"
+#include "ptx.cuh"
+#include "umma_nosw.cuh"
+
+namespace fitb200 {
+
+constexpr int A3_BQ = 128;                        // queries per unit
+constexpr int A3_BK = 128;                        // keys per block
+constexpr int A3_GROUP = 128;                     // threads of one softmax group (4 warps = the 4 TMEM lane quarters)
+constexpr int A3_THREADS = 128 + 2 * A3_GROUP;    // warps 0-1 producers, 2 MMA, 3 spare, 4-7 group 0, 8-11 group 1
+constexpr int A3_OCOL = 128;                      // O accumulator columns inside a group's TMEM region
+constexpr int A3_NS = 2;                          // K / V ring stages per group
+
+__device__ __forceinline__ void a3_tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];\n" ::"l"(reinterpret_cast<uint64_t>(m)),
+               "r"(ptx::smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+
+template <int HD>
+struct A3Cfg {
+  static constexpr int DP = (HD + 15) / 16 * 16;      // contraction width of q.k^T and N of p.v (72 -> 80)
+  static constexpr int CHP = DP / 8, CH = HD / 8;
+  static constexpr int CS = 128 * 16;                  // chunk-column stride inside a 128-row block
+  static constexpr int BLOCK = CHP * CS;               // bytes of one 128-row operand block (incl. the contraction pad chunk)
+  static constexpr int Q_OFF = 0;                      // [2 groups]
+  static constexpr int KV_OFF = 2 * BLOCK;             // [2 groups][A3_NS][K, V]
+  static constexpr int BAR_OFF = KV_OFF + 2 * A3_NS * 2 * BLOCK;
+  static constexpr int NBARS_G = 2 + 4 * A3_NS + 4;    // q_full q_empty | k_full v_full k_empty v_empty [NS] | s_full p_ready o_full t_empty
+  static constexpr int SMEM = BAR_OFF + 2 * NBARS_G * 8 + 16 + 1024 /*alignment slack*/;
+  static constexpr int OUT_ROW = HD * 2;               // staging row bytes (dense TMA box)
+};
+
+struct A3Unit { int r, head, q0, kvl, nkb; };
+
+// unit u = (item, query tile): item = (sample, head).  Returns false for padded query tiles (no tensor work, zero rows).
+__device__ __forceinline__ bool a3_decode(int u, int nq, int h, int Tn, const int32_t* __restrict__ kv_len, A3Unit& o) {
+  const int item = u / nq, qt = u - item * nq;
+  o.r = item / h; o.head = item - o.r * h;
+  o.kvl = min(kv_len[o.r], Tn);
+  o.q0 = qt * A3_BQ;
+  o.nkb = (o.kvl + A3_BK - 1) / A3_BK;
+  return o.q0 < o.kvl;
+}
+
+template <int HD>
+__global__ void __launch_bounds__(A3_THREADS, 1)
+attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmOut, const int32_t* __restrict__ kv_len,
+                const uint8_t* __restrict__ mask, int R, int Tn, int h, __nv_bfloat16* __restrict__ out, float* __restrict__ lse) {
+  using C = A3Cfg<HD>;
+  constexpr int DP = C::DP, CH = C::CH, CS = C::CS, BLOCK = C::BLOCK, NB = C::NBARS_G;
+  extern __shared__ uint8_t a3_raw[];
+  uint8_t* sm = a3_raw + ((1024u - (ptx::smem_u32(a3_raw) & 1023u)) & 1023u);
+  uint8_t* sQ = sm + C::Q_OFF;
+  uint8_t* sKV = sm + C::KV_OFF;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + C::BAR_OFF);
+  // barrier g-th group: base = bars + g * NB
+  auto q_full = [&](int g) { return bars + g * NB; };
+  auto q_empty = [&](int g) { return bars + g * NB + 1; };
+  auto k_full = [&](int g, int s) { return bars + g * NB + 2 + s; };
+  auto v_full = [&](int g, int s) { return bars + g * NB + 2 + A3_NS + s; };
+  auto k_empty = [&](int g, int s) { return bars + g * NB + 2 + 2 * A3_NS + s; };
+  auto v_empty = [&](int g, int s) { return bars + g * NB + 2 + 3 * A3_NS + s; };
+  auto s_full = [&](int g) { return bars + g * NB + 2 + 4 * A3_NS; };
+  auto p_ready = [&](int g) { return bars + g * NB + 3 + 4 * A3_NS; };
+  auto o_full = [&](int g) { return bars + g * NB + 4 + 4 * A3_NS; };
+  auto t_empty = [&](int g) { return bars + g * NB + 5 + 4 * A3_NS; };
+  auto kbuf = [&](int g, int s) { return sKV + ((g * A3_NS + s) * 2) * BLOCK; };
+  auto vbuf = [&](int g, int s) { return sKV + ((g * A3_NS + s) * 2 + 1) * BLOCK; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NB);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nq = (Tn + A3_BQ - 1) / A3_BQ;  // query units per item
+  const int U = R * h * nq;
+  const int D = h * HD;
+
+  if (tid == 0) {
+    ptx::prefetch_tmap(&tmQKV);
+    ptx::prefetch_tmap(&tmOut);
+    for (int g = 0; g < 2; ++g) {
+      ptx::mbar_init(q_full(g), 1); ptx::mbar_init(q_empty(g), 4);  // 4 = the storing warps
+      for (int s = 0; s < A3_NS; ++s) {
+        ptx::mbar_init(k_full(g, s), 1); ptx::mbar_init(v_full(g, s), 1); ptx::mbar_init(k_empty(g, s), 1); ptx::mbar_init(v_empty(g, s), 1);
+      }
+      ptx::mbar_init(s_full(g), 1); ptx::mbar_init(p_ready(g), A3_GROUP); ptx::mbar_init(o_full(g), 1); ptx::mbar_init(t_empty(g), A3_GROUP);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (DP != HD) {  // contraction padding (head_dim 72 -> 80) of every Q / K block: zeroed once, TMA boxes never touch it
+    for (int i = tid; i < (2 + 2 * A3_NS) * 128; i += A3_THREADS) {
+      const int b = i >> 7, rr = i & 127;
+      uint8_t* blk = b < 2 ? sQ + b * BLOCK : kbuf((b - 2) / A3_NS, (b - 2) % A3_NS);
+      *reinterpret_cast<uint4*>(blk + CH * CS + rr * 16) = make_uint4(0, 0, 0, 0);
+    }
+  }
+  if (warp == 2) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tb = *tmem_slot;
+  constexpr uint32_t BOX = CH * CS;  // bytes of one TMA box {8, 128, CH}
+
+  if (warp < 2) {
+    // ------------------------------------------------------------------------------------------ TMA producer of group `warp`
+    if (lane == 0) {
+      const int g = warp;
+      int ucnt = 0, bcnt = 0;
+      for (int u = blockIdx.x + g * gridDim.x; u < U; u += 2 * gridDim.x) {
+        A3Unit un;
+        if (!a3_decode(u, nq, h, Tn, kv_len, un)) continue;
+        const int row0 = un.r * Tn, cq = un.head * CH, ck = (D + un.head * HD) / 8, cv = (2 * D + un.head * HD) / 8;
+        ptx::mbar_wait(q_empty(g), (ucnt & 1) ^ 1);
+        ptx::mbar_arrive_expect_tx(q_full(g), BOX);
+        tma_load_3d(sQ + g * BLOCK, &tmQKV, q_full(g), 0, row0 + un.q0, cq);
+        for (int j = 0; j < un.nkb; ++j, ++bcnt) {
+          const int slot = bcnt % A3_NS; const uint32_t ph = (bcnt / A3_NS) & 1;
+          ptx::mbar_wait(k_empty(g, slot), ph ^ 1);
+          ptx::mbar_arrive_expect_tx(k_full(g, slot), BOX);
+          tma_load_3d(kbuf(g, slot), &tmQKV, k_full(g, slot), 0, row0 + j * A3_BK, ck);
+          ptx::mbar_wait(v_empty(g, slot), ph ^ 1);
+          ptx::mbar_arrive_expect_tx(v_full(g, slot), BOX);
+          tma_load_3d(vbuf(g, slot), &tmQKV, v_full(g, slot), 0, row0 + j * A3_BK, cv);
+        }
+        ++ucnt;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2) {
+    // ------------------------------------------------------------------------------------------ MMA issuer (both groups)
+    if (lane == 0) {
+      struct St { int u, nkb, kvl, j, stage, ucnt, bcnt; bool active; } st[2];
+      auto next_unit = [&](St& s, int g, int from) {
+        s.active = false;
+        for (int u = from; u < U; u += 2 * gridDim.x) {
+          A3Unit un;
+          if (a3_decode(u, nq, h, Tn, kv_len, un)) { s.u = u; s.nkb = un.nkb; s.kvl = un.kvl; s.j = 0; s.stage = 0; s.active = true; break; }
+        }
+      };
+      for (int g = 0; g < 2; ++g) { st[g].ucnt = 0; st[g].bcnt = 0; next_unit(st[g], g, blockIdx.x + g * gridDim.x); }
+      uint32_t spins = 0;
+      while (st[0].active || st[1].active) {
+        bool progressed = false;
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          St& s = st[g];
+          if (!s.active) continue;
+          const int slot = s.bcnt % A3_NS; const uint32_t ph = (s.bcnt / A3_NS) & 1;
+          const int nk16 = (min(A3_BK, s.kvl - s.j * A3_BK) + 15) & ~15;
+          const uint32_t tr = tb + g * 256;
+          if (s.stage == 0) {
+            if ((s.j > 0 || ptx::mbar_try_wait(q_full(g), s.ucnt & 1)) && ptx::mbar_try_wait(k_full(g, slot), ph)) {
+              ptx::tc_fence_after();
+              const uint32_t idesc = ptx::idesc_bf16_f32(A3_BQ, nk16);
+#pragma unroll
+              for (int k = 0; k < DP / 16; ++k) {
+                const uint64_t da = desc_nosw(ptx::smem_u32(sQ + g * BLOCK + 2 * k * CS), CS, 128);
+                const uint64_t db = desc_nosw(ptx::smem_u32(kbuf(g, slot) + 2 * k * CS), CS, 128);
+                ptx::mma_f16_ss(tr, da, db, idesc, k != 0);
+              }
+              ptx::mma_commit(s_full(g));
+              ptx::mma_commit(k_empty(g, slot));
+              s.stage = 1;
+              progressed = true;
+            }
+          } else {
+            // P_0 V_0 overwrites O: the previous unit's epilogue must have read it (t_empty)
+            if ((s.j > 0 || ptx::mbar_try_wait(t_empty(g), (s.ucnt & 1) ^ 1)) && ptx::mbar_try_wait(p_ready(g), s.bcnt & 1) &&
+                ptx::mbar_try_wait(v_full(g, slot), ph)) {
+              ptx::tc_fence_after();
+              const uint32_t idesc = ptx::idesc_bf16_f32(A3_BQ, DP) | (1u << 16);  // B (= V) is MN-major
+              const int ksteps = nk16 >> 4;
+              const uint8_t* v0 = vbuf(g, slot);
+              for (int k = 0; k < ksteps; ++k) {
+                const uint64_t db = desc_nosw(ptx::smem_u32(v0 + k * 256), 128, CS);
+                mma_f16_ts(tr + A3_OCOL, tr + 8 * k, db, idesc, (s.j > 0 || k > 0) ? 1u : 0u);
+              }
+              ptx::mma_commit(v_empty(g, slot));
+              ++s.bcnt;
+              if (++s.j == s.nkb) {
+                ptx::mma_commit(o_full(g));
+                ++s.ucnt;
+                next_unit(s, g, s.u + 2 * gridDim.x);
+              } else {
+                s.stage = 0;
+              }
+              progressed = true;
+            }
+          }
+        }
+        if (progressed) spins = 0;
+        else { if (++spins > (1u << 22)) __trap(); __nanosleep(32); }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------------------------------ softmax / epilogue groups
+    const int g = (warp - 4) >> 2;
+    const int gt = tid - 128 - g * A3_GROUP;       // thread inside the group
+    const int quarter = warp & 3;                  // TMEM lane quarter this warp may access
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_base = tb + g * 256 + ((uint32_t)(quarter * 32) << 16);
+    const float sl2 = rsqrtf((float)HD) * 1.4426950408889634f;  // softmax scale folded with log2(e)
+    int ucnt = 0, bcnt = 0;
+    for (int u = blockIdx.x + g * gridDim.x; u < U; u += 2 * gridDim.x) {
+      A3Unit un;
+      const bool live = a3_decode(u, nq, h, Tn, kv_len, un);
+      const int r = un.r, head = un.head, q0 = un.q0;
+      if (!live) {  // padded query tile: zero output rows, no tensor work
+        for (int i = gt; i < A3_BQ * CH; i += A3_GROUP) {
+          const int rw = i / CH, c = i - rw * CH;
+          if (q0 + rw < Tn) *reinterpret_cast<uint4*>(out + ((size_t)r * Tn + q0 + rw) * D + head * HD + c * 8) = make_uint4(0, 0, 0, 0);
+        }
+        if (lse) for (int i = gt; i < A3_BQ; i += A3_GROUP) if (q0 + i < Tn) lse[((size_t)r * h + head) * Tn + q0 + i] = 0.f;
+        continue;
+      }
+      float m_run = -INFINITY, l_run = 0.f;
+      for (int j = 0; j < un.nkb; ++j, ++bcnt) {
+        const int key0 = j * A3_BK;
+        const int nk = min(A3_BK, un.kvl - key0), nk16 = (nk + 15) & ~15;
+        const int nch = (nk16 + 31) >> 5;
+        // key validity words (warp-uniform registers): bit i of vw[c] = key key0 + 32 c + i is < kv_len and not masked out
+        uint32_t vw[4];
+        {
+          bool ok[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int key = c * 32 + lane;
+            ok[c] = key < nk && (mask == nullptr || mask[(size_t)r * Tn + key0 + key] != 0);
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) vw[c] = __ballot_sync(0xffffffffu, ok[c]);
+        }
+        ptx::mbar_wait(s_full(g), bcnt & 1);
+        ptx::tc_fence_after();
+        float m = m_run;
+        uint32_t sbuf[2][32];
+        tmem_ld32(lane_base, sbuf[0]);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c < nch) {
+            ptx::tmem_ld_wait();
+            if (c + 1 < nch) tmem_ld32(lane_base + (c + 1) * 32, sbuf[(c + 1) & 1]);
+            const uint32_t w = vw[c];
+            if (w == 0xffffffffu) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) m = fmaxf(m, __uint_as_float(sbuf[c & 1][i]));
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) m = (w >> i) & 1u ? fmaxf(m, __uint_as_float(sbuf[c & 1][i])) : m;
+            }
+          }
+        }
+        const float msc = (m == -INFINITY ? 0.f : m) * sl2;
+        const float alpha = ex2f(fmaf(m_run, sl2, -msc));  // m_run = -inf (first block / all keys so far masked) -> 0
+        const bool moved = m != m_run;
+        float sum = 0.f;
+        // P (bf16 pairs) of chunk c goes to columns [16 c, 16 c + 16): inside S chunk c / 2, which this thread has already consumed
+        tmem_ld32(lane_base, sbuf[0]);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c < nch) {
+            ptx::tmem_ld_wait();
+            if (c + 1 < nch) tmem_ld32(lane_base + (c + 1) * 32, sbuf[(c + 1) & 1]);
+            const uint32_t w = vw[c];
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              float p0 = ex2f(fmaf(__uint_as_float(sbuf[c & 1][2 * i]), sl2, -msc));
+              float p1 = ex2f(fmaf(__uint_as_float(sbuf[c & 1][2 * i + 1]), sl2, -msc));
+              if (w != 0xffffffffu) {
+                p0 = (w >> (2 * i)) & 1u ? p0 : 0.f;
+                p1 = (w >> (2 * i + 1)) & 1u ? p1 : 0.f;
+              }
+              sum += p0 + p1;
+              pk[i] = pack_bf16x2(p0, p1);
+            }
+            tmem_st16(lane_base + c * 16, pk);
+          }
+        }
+        l_run = fmaf(l_run, alpha, sum);
+        m_run = m;
+        // O row *= alpha (P_{j-1} V_{j-1} has retired: s_full of this block was committed behind it).  Skipped when no row of the
+        // warp saw a new maximum (alpha == 1 for all of them), which is the common case after the first blocks.
+        if (j > 0 && __any_sync(0xffffffffu, moved)) {
+#pragma unroll
+          for (int cb = 0; cb < DP / 16; ++cb) {
+            uint32_t o[16];
+            ptx::tmem_ld16(lane_base + A3_OCOL + cb * 16, o);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st16(lane_base + A3_OCOL + cb * 16, o);
+          }
+        }
+        tmem_st_wait();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(p_ready(g));
+      }
+
+      // ---- epilogue: O / rowsum -> bf16 -> staging (the unit's Q buffer, consumed by every S_j) -> one TMA store per warp (32 rows)
+      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+      uint8_t* stg = sQ + g * BLOCK + row * C::OUT_ROW;
+      const uint32_t swz = HD == 64 ? (uint32_t)(row & 7) : 0u;  // 128-byte rows: 128B-swizzled box (conflict-free 16-byte stores)
+      ptx::mbar_wait(o_full(g), ucnt & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int cb = 0; cb < 2; ++cb) {
+        uint32_t o[32];
+        tmem_ld32(lane_base + A3_OCOL + cb * 32, o);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 v;
+          v.x = pack_bf16x2(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
+          v.y = pack_bf16x2(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
+          v.z = pack_bf16x2(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
+          v.w = pack_bf16x2(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
+          *reinterpret_cast<uint4*>(stg + (((uint32_t)(cb * 4 + q) ^ swz) << 4)) = v;
+        }
+      }
+      if (HD == 72) {  // columns [64, 72)
+        uint32_t o2[16];
+        ptx::tmem_ld16(lane_base + A3_OCOL + 64, o2);
+        ptx::tmem_ld_wait();
+        uint4 v;
+        v.x = pack_bf16x2(__uint_as_float(o2[0]) * inv, __uint_as_float(o2[1]) * inv);
+        v.y = pack_bf16x2(__uint_as_float(o2[2]) * inv, __uint_as_float(o2[3]) * inv);
+        v.z = pack_bf16x2(__uint_as_float(o2[4]) * inv, __uint_as_float(o2[5]) * inv);
+        v.w = pack_bf16x2(__uint_as_float(o2[6]) * inv, __uint_as_float(o2[7]) * inv);
+        *reinterpret_cast<uint4*>(stg + (8 << 4)) = v;
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(t_empty(g));  // O free for P_0 V_0 of this group's next unit
+      if (lse && q0 + row < Tn)
+        lse[((size_t)r * h + head) * Tn + q0 + row] = l_run > 0.f ? (m_run * sl2 + log2f(l_run)) * 0.6931471805599453f : 0.f;
+      ptx::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        a3_tma_store_3d(&tmOut, sQ + g * BLOCK + quarter * 32 * C::OUT_ROW, head * HD, q0 + quarter * 32, r);
+        ptx::tma_store_commit();
+        ptx::tma_store_wait_read<0>();       // the staging is the group's only Q buffer: release it as soon as the store has read it
+        ptx::mbar_arrive(q_empty(g));
+      }
+      ++ucnt;
+    }
+    if (lane == 0) ptx::tma_store_wait_all();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tb, 512);
+  }
+}
+
+template <int HD>
+static int launch_attn_tc3(const void* qkv, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, void* out, float* lse, cudaStream_t s) {
+  using C = A3Cfg<HD>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(attn_tc3_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    if (e != cudaSuccess) { set_last_error("attn_tc3: cannot set %d bytes of dynamic smem: %s", C::SMEM, cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
+    attr_done = true;
+  }
+  CUtensorMap tmQ, tmO;
+  const int D = h * HD;
+  if (at_make_tmap3(&tmQ, qkv, (long)R * Tn, 3L * D, C::CH) != 0) { set_last_error("attn_tc3: cuTensorMapEncodeTiled (qkv) failed"); return FITB200_ERR_CUDA; }
+  {
+    // out [R, Tn, D] bf16: box {HD columns, 32 tokens, 1 sample}; rows beyond the sample's Tn tokens are clipped by the store
+    AtEncodeTiledFn enc = at_get_encode();
+    if (!enc) { set_last_error("attn_tc3: cuTensorMapEncodeTiled not available from the driver"); return FITB200_ERR_CUDA; }
+    cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)Tn, (cuuint64_t)R};
+    cuuint64_t strides[2] = {(cuuint64_t)D * 2, (cuuint64_t)Tn * D * 2};
+    cuuint32_t box[3] = {(cuuint32_t)HD, 32, 1};  // one store per warp: its 32 query rows
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult rc = enc(&tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      HD == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) { set_last_error("attn_tc3: cuTensorMapEncodeTiled (out) failed (%d)", (int)rc); return FITB200_ERR_CUDA; }
+  }
+  const int nq = (Tn + A3_BQ - 1) / A3_BQ;
+  const long units = (long)R * h * nq;
+  const int grid = units < sm_count() ? (int)units : sm_count();
+  attn_tc3_kernel<HD><<<grid, A3_THREADS, C::SMEM, s>>>(tmQ, tmO, kv_len, mask, R, Tn, h, (__nv_bfloat16*)out, lse);
+  FITB200_CHECK_LAUNCH("attn_tc3");
+  return FITB200_OK;
+}
+
+// bf16, any T, q / k prerotated.  Returns FITB200_ERR_UNSUPPORTED for other head dims (caller falls back to attn_mma.cu).
+int attn_fwd_tc3(const void* qkv, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s) {
+  if (d == 64) return launch_attn_tc3<64>(qkv, kv_len, mask, R, Tn, h, out, lse, s);
+  if (d == 72) return launch_attn_tc3<72>(qkv, kv_len, mask, R, Tn, h, out, lse, s);
+  return FITB200_ERR_UNSUPPORTED;
+}
+
+}  // namespace fitb200

@@ -301,3 +301,37 @@ def test_attention_persistent_many_items(ops, h, d):
             assert rel_l2(out[r, :L], want[r, :L]) < 5e-3, (r, L)
         q0 = (L + 127) // 128 * 128
         assert float(out[r, q0:].abs().max()) == 0.0 if q0 < T else True   # query tiles beyond kv_len are zero rows
+
+
+@pytest.mark.parametrize("T,h,d,nonprefix", [(400, 16, 72, False), (1000, 3, 72, True), (640, 4, 64, False), (300, 2, 64, True)])
+def test_attention_kv_blocked_long(ops, T, h, d, nonprefix):
+    """attn_tc3 (T > 256, pre-rotated q / k: the extrapolation shapes of BASELINE config 5): online softmax over 128-key blocks with
+    O rescaled in TMEM, ragged key counts around every block boundary (0 = item skipped, 1, 128, 129, 256, 257, T - 1, T), a
+    non-prefix mask, ring / phase drift over many units per CTA, and the saved log-sum-exp."""
+    g = torch.Generator().manual_seed(T + d)
+    base = [T, 0, 1, 128, 129, 256, 257, T - 1, 17, 385 if T > 385 else T - 3]
+    lens = base + [int(x) for x in torch.randint(0, T + 1, (14,), generator=g)]
+    R = len(lens)
+    qkv, freqs, mask = _attn_case(R, T, h, d, lens, seed=5, nonprefix=nonprefix)
+    # scores with a spread large enough that the running maximum keeps moving between blocks
+    qkv[:, :, 0] *= 2.0
+    q3, k3, v3 = qkv.bfloat16().float().permute(2, 0, 3, 1, 4)
+    qr, kr = fo.rope_rotate(q3, freqs).bfloat16().float(), fo.rope_rotate(k3, freqs).bfloat16().float()
+    want = fo.attention_core(qr, kr, v3, mask).transpose(1, 2).reshape(R, T, -1)
+    sc = (qr @ kr.transpose(-1, -2)) * d ** -0.5
+    want_lse = torch.logsumexp(sc.masked_fill(~mask[:, None, None, :], float("-inf")), -1)
+    qkv_rot = torch.stack([qr, kr, v3], 0).permute(1, 3, 0, 2, 4).contiguous().bfloat16()
+    kv, _ = ops.mask_to_kvlen(mask.cuda())
+    out = torch.full((R * T, h * d), float("nan"), dtype=torch.bfloat16, device="cuda")
+    lse = torch.full((R, h, T), float("nan"), device="cuda")
+    ops.attention(qkv_rot.cuda().view(R * T, 3 * h * d), None, kv, mask.cuda(), R, T, h, d, out, lse, prerotated=True)
+    assert bool(torch.isfinite(out.float()).all()) and bool(torch.isfinite(lse).all())   # every row written, padded ones included
+    out = out.float().cpu().view(R, T, h * d)
+    for r, L in enumerate(lens):
+        Lm = int(mask[r].sum())
+        if Lm > 0:
+            assert rel_l2(out[r, :L], want[r, :L]) < 5e-3, (r, L)
+            assert (lse[r, :, :L].cpu() - want_lse[r, :, :L]).abs().max() < 3e-2, (r, L)
+        q0 = (L + 127) // 128 * 128
+        if q0 < T:
+            assert float(out[r, q0:].abs().max()) == 0.0   # query tiles beyond kv_len are zero rows
