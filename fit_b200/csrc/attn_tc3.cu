@@ -163,25 +163,10 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         for (int g = 0; g < 2; ++g) {
           St& s = st[g];
           if (!s.active) continue;
-          const int slot = s.bcnt % A3_NS; const uint32_t ph = (s.bcnt / A3_NS) & 1;
-          const int nk16 = (min(A3_BK, s.kvl - s.j * A3_BK) + 15) & ~15;
           const uint32_t tr = tb + g * 256;
-          if (s.stage == 0) {
-            if ((s.j > 0 || ptx::mbar_try_wait(q_full(g), s.ucnt & 1)) && ptx::mbar_try_wait(k_full(g, slot), ph)) {
-              ptx::tc_fence_after();
-              const uint32_t idesc = ptx::idesc_bf16_f32(A3_BQ, nk16);
-#pragma unroll
-              for (int k = 0; k < DP / 16; ++k) {
-                const uint64_t da = desc_nosw(ptx::smem_u32(sQ + g * BLOCK + 2 * k * CS), CS, 128);
-                const uint64_t db = desc_nosw(ptx::smem_u32(kbuf(g, slot) + 2 * k * CS), CS, 128);
-                ptx::mma_f16_ss(tr, da, db, idesc, k != 0);
-              }
-              ptx::mma_commit(s_full(g));
-              ptx::mma_commit(k_empty(g, slot));
-              s.stage = 1;
-              progressed = true;
-            }
-          } else {
+          if (s.stage == 1) {
+            const int slot = s.bcnt % A3_NS; const uint32_t ph = (s.bcnt / A3_NS) & 1;
+            const int nk16 = (min(A3_BK, s.kvl - s.j * A3_BK) + 15) & ~15;
             // P_0 V_0 overwrites O: the previous unit's epilogue must have read it (t_empty)
             if ((s.j > 0 || ptx::mbar_try_wait(t_empty(g), (s.ucnt & 1) ^ 1)) && ptx::mbar_try_wait(p_ready(g), s.bcnt & 1) &&
                 ptx::mbar_try_wait(v_full(g, slot), ph)) {
@@ -202,6 +187,27 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
               } else {
                 s.stage = 0;
               }
+              progressed = true;
+            }
+          }
+          // S_{j+1} goes out right behind P_j V_j of the SAME group (not after the other group's turn): the group that finished its
+          // softmax first gets its next scores first, which keeps the two groups in anti-phase -- one multiplies while the other
+          // exponentiates.  Serving the groups strictly in turn interleaved PV(g1) PV(g0) S(g1) S(g0) and locked them in step.
+          if (s.active && s.stage == 0) {
+            const int slot = s.bcnt % A3_NS; const uint32_t ph = (s.bcnt / A3_NS) & 1;
+            const int nk16 = (min(A3_BK, s.kvl - s.j * A3_BK) + 15) & ~15;
+            if ((s.j > 0 || ptx::mbar_try_wait(q_full(g), s.ucnt & 1)) && ptx::mbar_try_wait(k_full(g, slot), ph)) {
+              ptx::tc_fence_after();
+              const uint32_t idesc = ptx::idesc_bf16_f32(A3_BQ, nk16);
+#pragma unroll
+              for (int k = 0; k < DP / 16; ++k) {
+                const uint64_t da = desc_nosw(ptx::smem_u32(sQ + g * BLOCK + 2 * k * CS), CS, 128);
+                const uint64_t db = desc_nosw(ptx::smem_u32(kbuf(g, slot) + 2 * k * CS), CS, 128);
+                ptx::mma_f16_ss(tr, da, db, idesc, k != 0);
+              }
+              ptx::mma_commit(s_full(g));
+              ptx::mma_commit(k_empty(g, slot));
+              s.stage = 1;
               progressed = true;
             }
           }
