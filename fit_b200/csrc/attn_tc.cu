@@ -358,6 +358,7 @@ static int launch_attn_tc(const void* qkv, const float* freqs, int freqs_rows, c
 }
 
 int attn_fwd_tc2(const void* qkv, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s);
+int attn_fwd_tc3(const void* qkv, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d, void* out, float* lse, cudaStream_t s);
 
 // bf16, T <= 256: the tcgen05 kernel.  Called from fitb200_attn_fwd (attn_mma.cu).  prerotated: q, k already carry the RoPE.
 int attn_fwd_tc(const void* qkv, const float* freqs, int freqs_rows, const int32_t* kv_len, const uint8_t* mask, int R, int Tn, int h, int d,
@@ -366,6 +367,9 @@ int attn_fwd_tc(const void* qkv, const float* freqs, int freqs_rows, const int32
     if (((uintptr_t)qkv & 15) != 0) { set_last_error("attn_fwd: qkv must be 16-byte aligned"); return FITB200_ERR_INVALID_ARG; }
     // persistent warp-specialised schedule (attn_tc2.cu); FITB200_ATTN_V1=1 keeps the one-tile-per-CTA kernel below
     static const bool v1 = [] { const char* e = getenv("FITB200_ATTN_V1"); return e && e[0] == '1'; }();
+    // FITB200_ATTN_TC3=1: the KV-blocked kernel of the long sequences (attn_tc3.cu) on these shapes too (A/B timing)
+    static const bool v3 = [] { const char* e = getenv("FITB200_ATTN_TC3"); return e && e[0] == '1'; }();
+    if (v3 && (d == 64 || d == 72) && ((uintptr_t)out & 15) == 0) return attn_fwd_tc3(qkv, kv_len, mask, R, Tn, h, d, out, lse, s);
     if (!v1 && (d == 64 || d == 72) && ((uintptr_t)out & 15) == 0) return attn_fwd_tc2(qkv, kv_len, mask, R, Tn, h, d, out, lse, s);
     if (d == 64) return launch_attn_tc<64, true>(qkv, freqs, freqs_rows, kv_len, mask, R, Tn, h, out, lse, s);
     if (d == 72) return launch_attn_tc<72, true>(qkv, freqs, freqs_rows, kv_len, mask, R, Tn, h, out, lse, s);
