@@ -5,10 +5,13 @@
 // (persistent CTAs, event-driven MMA issuer, row-per-thread softmax groups) extended by a key loop:
 //   warps 0, 1  TMA producers of group 0 / 1: per 128-query unit Q once, then K_j / V_j blocks of 128 keys through a 2-stage ring
 //   warp 2      MMA issuer for both groups: S_j = Q K_j^T (TMEM region g, columns [0, 128)), then O += P_j V_j (columns [128, 128+DP))
-//   warps 4-7   softmax / epilogue group 0, warps 8-11 group 1: each group owns one unit at a time; one thread = one query row:
-//               pass 1 block max, pass 2 P_j = exp2(S_j - max) as bf16 over the S columns it came from, O row rescaled in TMEM when
-//               the running max moved (skipped per warp when no row's did), at the end O / rowsum -> staging (the unit's Q buffer)
-//               -> one TMA store per warp (rows clipped at the sample's token count by the 3-D map).
+//   warps 4-11  softmax / epilogue group 0, warps 12-19 group 1: each group owns one unit at a time; two threads per query row
+//               (TMEM lane quarter = warp & 3, key half = 64 of the block's 128 keys): block max (halves exchanged through shared
+//               memory, one named barrier per block), P_j = exp2(S_j - max) as bf16 written over the first 32 of the thread's own 64
+//               score columns (keys [0,64) -> columns [0,32), keys [64,128) -> columns [64,96)), partial row sums joined at the end,
+//               O row rescaled in TMEM (columns split between the halves) when the reference max moved (skipped per warp when no
+//               row's did), at the end O / rowsum -> staging (the unit's Q buffer) -> TMA stores of 32 rows (rows clipped at the
+//               sample's token count by the 3-D map).
 // The two groups interleave on the tensor pipe: while one runs its softmax the other's S / PV multiply.  tcgen05.mma executes in
 // issue order, so S_{j+1} (which overwrites P_j) is simply issued behind P_j V_j; the only waits the issuer has are data (TMA) and
 // p_ready.  Only keys < kv_len are multiplied (N / K of a block = round16 of its live keys); query tiles at or beyond kv_len are
@@ -23,8 +26,8 @@ namespace fitb200 {
 
 constexpr int A3_BQ = 128;                        // queries per unit
 constexpr int A3_BK = 128;                        // keys per block
-constexpr int A3_GROUP = 128;                     // threads of one softmax group (4 warps = the 4 TMEM lane quarters)
-constexpr int A3_THREADS = 128 + 2 * A3_GROUP;    // warps 0-1 producers, 2 MMA, 3 spare, 4-7 group 0, 8-11 group 1
+constexpr int A3_GROUP = 256;                     // threads of one softmax group: 8 warps = 4 TMEM lane quarters x 2 key halves
+constexpr int A3_THREADS = 128 + 2 * A3_GROUP;    // warps 0-1 producers, 2 MMA, 3 spare, 4-11 group 0, 12-19 group 1
 constexpr int A3_OCOL = 128;                      // O accumulator columns inside a group's TMEM region
 constexpr float A3_TAU = 8.f;                      // log2 of the growth of the row maximum that triggers a rescale of O
 constexpr int A3_NS = 2;                          // K / V ring stages per group
@@ -45,7 +48,9 @@ struct A3Cfg {
   static constexpr int KV_OFF = 2 * BLOCK;             // [2 groups][A3_NS][K, V]
   static constexpr int BAR_OFF = KV_OFF + 2 * A3_NS * 2 * BLOCK;
   static constexpr int NBARS_G = 2 + 4 * A3_NS + 4;    // q_full q_empty | k_full v_full k_empty v_empty [NS] | s_full p_ready o_full t_empty
-  static constexpr int SMEM = BAR_OFF + 2 * NBARS_G * 8 + 16 + 1024 /*alignment slack*/;
+  static constexpr int SCR_OFF = BAR_OFF + 2 * NBARS_G * 8 + 16;   // per group: block max [2 parities][2 halves][128] + row sum [2][128]
+  static constexpr int SCR_BYTES = 6 * 128 * 4;
+  static constexpr int SMEM = SCR_OFF + 2 * SCR_BYTES + 1024 /*alignment slack*/;
   static constexpr int OUT_ROW = HD * 2;               // staging row bytes (dense TMA box)
 };
 
@@ -96,7 +101,7 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     ptx::prefetch_tmap(&tmQKV);
     ptx::prefetch_tmap(&tmOut);
     for (int g = 0; g < 2; ++g) {
-      ptx::mbar_init(q_full(g), 1); ptx::mbar_init(q_empty(g), 4);  // 4 = the storing warps
+      ptx::mbar_init(q_full(g), 1); ptx::mbar_init(q_empty(g), 1);
       for (int s = 0; s < A3_NS; ++s) {
         ptx::mbar_init(k_full(g, s), 1); ptx::mbar_init(v_full(g, s), 1); ptx::mbar_init(k_empty(g, s), 1); ptx::mbar_init(v_empty(g, s), 1);
       }
@@ -176,7 +181,8 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
               const uint8_t* v0 = vbuf(g, slot);
               for (int k = 0; k < ksteps; ++k) {
                 const uint64_t db = desc_nosw(ptx::smem_u32(v0 + k * 256), 128, CS);
-                mma_f16_ts(tr + A3_OCOL, tr + 8 * k, db, idesc, (s.j > 0 || k > 0) ? 1u : 0u);
+                // P of keys [0, 64) sits in columns [0, 32), P of keys [64, 128) in columns [64, 96) (each key half over its own scores)
+                mma_f16_ts(tr + A3_OCOL, tr + (k < 4 ? 8 * k : 64 + 8 * (k - 4)), db, idesc, (s.j > 0 || k > 0) ? 1u : 0u);
               }
               ptx::mma_commit(v_empty(g, slot));
               ++s.bcnt;
@@ -219,12 +225,17 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     __syncwarp();
   } else if (warp >= 4) {
     // ------------------------------------------------------------------------------------------ softmax / epilogue groups
-    const int g = (warp - 4) >> 2;
+    const int g = (warp - 4) >> 3;                 // group 0: warps 4-11, group 1: warps 12-19
     const int gt = tid - 128 - g * A3_GROUP;       // thread inside the group
-    const int quarter = warp & 3;                  // TMEM lane quarter this warp may access
+    const int gw = gt >> 5;                        // warp inside the group
+    const int quarter = warp & 3, half = gw >> 2;  // TMEM lane quarter this warp may access; which 64 keys of a block / which O columns
     const int row = quarter * 32 + lane;
+    float* smax = reinterpret_cast<float*>(sm + C::SCR_OFF + g * C::SCR_BYTES);  // [2][2][128]
+    float* ssum = smax + 4 * A3_BQ;                                                // [2][128]
     const uint32_t lane_base = tb + g * 256 + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t my_base = lane_base + half * 64;  // this thread's 64 score columns; its P goes over the first 32 of them
     const float sl2 = rsqrtf((float)HD) * 1.4426950408889634f;  // softmax scale folded with log2(e)
+    const int bar_id = 1 + g;
     int ucnt = 0, bcnt = 0;
     for (int u = blockIdx.x + g * gridDim.x; u < U; u += 2 * gridDim.x) {
       A3Unit un;
@@ -238,43 +249,47 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         if (lse) for (int i = gt; i < A3_BQ; i += A3_GROUP) if (q0 + i < Tn) lse[((size_t)r * h + head) * Tn + q0 + i] = 0.f;
         continue;
       }
-      float m_run = -INFINITY, l_run = 0.f;
+      float m_run = -INFINITY, l_run = 0.f;   // l_run: this thread's half of the row sum (both halves use the same reference maximum)
       for (int j = 0; j < un.nkb; ++j, ++bcnt) {
-        const int key0 = j * A3_BK;
-        const int nk = min(A3_BK, un.kvl - key0), nk16 = (nk + 15) & ~15;
-        const int nch = (nk16 + 31) >> 5;
+        const int key0 = j * A3_BK + half * 64;
+        const int nk = min(A3_BK, un.kvl - j * A3_BK), nk16 = (nk + 15) & ~15;
+        const int n_my = max(0, min(nk16 - half * 64, 64));
+        const int nch = (n_my + 31) >> 5;
         // key validity words (warp-uniform registers): bit i of vw[c] = key key0 + 32 c + i is < kv_len and not masked out
-        uint32_t vw[4];
+        uint32_t vw[2];
         {
-          bool ok[4];
+          bool ok[2];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const int key = c * 32 + lane;
-            ok[c] = key < nk && (mask == nullptr || mask[(size_t)r * Tn + key0 + key] != 0);
+          for (int c = 0; c < 2; ++c) {
+            const int key = key0 + c * 32 + lane;
+            ok[c] = key < un.kvl && (mask == nullptr || mask[(size_t)r * Tn + key] != 0);
           }
 #pragma unroll
-          for (int c = 0; c < 4; ++c) vw[c] = __ballot_sync(0xffffffffu, ok[c]);
+          for (int c = 0; c < 2; ++c) vw[c] = __ballot_sync(0xffffffffu, ok[c]);
         }
         ptx::mbar_wait(s_full(g), bcnt & 1);
         ptx::tc_fence_after();
-        float m = m_run;
-        uint32_t sbuf[2][32];
-        tmem_ld32(lane_base, sbuf[0]);
+        float m = -INFINITY;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           if (c < nch) {
+            uint32_t sb[32];
+            tmem_ld32(my_base + c * 32, sb);
             ptx::tmem_ld_wait();
-            if (c + 1 < nch) tmem_ld32(lane_base + (c + 1) * 32, sbuf[(c + 1) & 1]);
             const uint32_t w = vw[c];
             if (w == 0xffffffffu) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) m = fmaxf(m, __uint_as_float(sbuf[c & 1][i]));
+              for (int i = 0; i < 32; ++i) m = fmaxf(m, __uint_as_float(sb[i]));
             } else {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) m = (w >> i) & 1u ? fmaxf(m, __uint_as_float(sbuf[c & 1][i])) : m;
+              for (int i = 0; i < 32; ++i) m = (w >> i) & 1u ? fmaxf(m, __uint_as_float(sb[i])) : m;
             }
           }
         }
+        float* sx = smax + (bcnt & 1) * 2 * A3_BQ;
+        sx[half * A3_BQ + row] = m;
+        ptx::named_bar_sync(bar_id, A3_GROUP);
+        m = fmaxf(m_run, fmaxf(sx[row], sx[A3_BQ + row]));
         // Lazy rescaling: the reference maximum only follows the true one when that grew by more than 2^A3_TAU (exact in the end:
         // the normalisation cancels whatever reference was used; P <= 2^A3_TAU stays far inside bf16 / fp32 range).  With it O is
         // rescaled on the first blocks only; following every new maximum rescaled O on 82 % of the blocks (ncu, T = 4096).
@@ -283,42 +298,52 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const float msc = (m == -INFINITY ? 0.f : m) * sl2;
         const float alpha = moved ? ex2f(fmaf(m_run, sl2, -msc)) : 1.f;  // m_run = -inf (first block / all keys so far masked) -> 0
         float sum = 0.f;
-        // P (bf16 pairs) of chunk c goes to columns [16 c, 16 c + 16): inside S chunk c / 2, which this thread has already consumed
-        tmem_ld32(lane_base, sbuf[0]);
+        // P (bf16 pairs) of chunk c goes to columns [16 c, 16 c + 16) of this thread's own score columns: already consumed by it
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           if (c < nch) {
+            uint32_t sb[32];
+            tmem_ld32(my_base + c * 32, sb);
             ptx::tmem_ld_wait();
-            if (c + 1 < nch) tmem_ld32(lane_base + (c + 1) * 32, sbuf[(c + 1) & 1]);
             const uint32_t w = vw[c];
             uint32_t pk[16];
+            if (w == 0xffffffffu) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              float p0 = ex2f(fmaf(__uint_as_float(sbuf[c & 1][2 * i]), sl2, -msc));
-              float p1 = ex2f(fmaf(__uint_as_float(sbuf[c & 1][2 * i + 1]), sl2, -msc));
-              if (w != 0xffffffffu) {
+              for (int i = 0; i < 16; ++i) {
+                const float p0 = ex2f(fmaf(__uint_as_float(sb[2 * i]), sl2, -msc));
+                const float p1 = ex2f(fmaf(__uint_as_float(sb[2 * i + 1]), sl2, -msc));
+                sum += p0 + p1;
+                pk[i] = pack_bf16x2(p0, p1);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                float p0 = ex2f(fmaf(__uint_as_float(sb[2 * i]), sl2, -msc));
+                float p1 = ex2f(fmaf(__uint_as_float(sb[2 * i + 1]), sl2, -msc));
                 p0 = (w >> (2 * i)) & 1u ? p0 : 0.f;
                 p1 = (w >> (2 * i + 1)) & 1u ? p1 : 0.f;
+                sum += p0 + p1;
+                pk[i] = pack_bf16x2(p0, p1);
               }
-              sum += p0 + p1;
-              pk[i] = pack_bf16x2(p0, p1);
             }
-            tmem_st16(lane_base + c * 16, pk);
+            tmem_st16(my_base + c * 16, pk);
           }
         }
         l_run = fmaf(l_run, alpha, sum);
         m_run = m;
-        // O row *= alpha (P_{j-1} V_{j-1} has retired: s_full of this block was committed behind it).  Skipped when no row of the
-        // warp saw a new maximum (alpha == 1 for all of them), which is the common case after the first blocks.
+        // O row *= alpha (P_{j-1} V_{j-1} has retired: s_full of this block was committed behind it); half 0 takes columns [0, 48),
+        // half 1 the rest.  Skipped when no row of the warp moved its reference maximum (the common case after the first blocks).
         if (j > 0 && __any_sync(0xffffffffu, moved)) {
 #pragma unroll
           for (int cb = 0; cb < DP / 16; ++cb) {
-            uint32_t o[16];
-            ptx::tmem_ld16(lane_base + A3_OCOL + cb * 16, o);
-            ptx::tmem_ld_wait();
+            if ((cb < 3) == (half == 0)) {
+              uint32_t o[16];
+              ptx::tmem_ld16(lane_base + A3_OCOL + cb * 16, o);
+              ptx::tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st16(lane_base + A3_OCOL + cb * 16, o);
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st16(lane_base + A3_OCOL + cb * 16, o);
+            }
           }
         }
         tmem_st_wait();
@@ -326,53 +351,64 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         ptx::mbar_arrive(p_ready(g));
       }
 
-      // ---- epilogue: O / rowsum -> bf16 -> staging (the unit's Q buffer, consumed by every S_j) -> one TMA store per warp (32 rows)
-      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-      uint8_t* stg = sQ + g * BLOCK + row * C::OUT_ROW;
-      const uint32_t swz = HD == 64 ? (uint32_t)(row & 7) : 0u;  // 128-byte rows: 128B-swizzled box (conflict-free 16-byte stores)
+      // ---- epilogue: O / rowsum -> bf16 -> staging (the unit's Q buffer, consumed by every S_j) -> TMA stores (32 rows each)
+      ssum[half * A3_BQ + row] = l_run;
       ptx::mbar_wait(o_full(g), ucnt & 1);
       ptx::tc_fence_after();
-#pragma unroll
-      for (int cb = 0; cb < 2; ++cb) {
+      ptx::named_bar_sync(bar_id, A3_GROUP);
+      const float l = ssum[row] + ssum[A3_BQ + row];
+      const float inv = l > 0.f ? 1.f / l : 0.f;
+      constexpr int C0 = HD == 64 ? 32 : 48;  // columns [0, C0) -> half 0, [C0, HD) -> half 1
+      uint8_t* stg = sQ + g * BLOCK + row * C::OUT_ROW;
+      const uint32_t swz = HD == 64 ? (uint32_t)(row & 7) : 0u;  // 128-byte rows: 128B-swizzled box (conflict-free 16-byte stores)
+      {
         uint32_t o[32];
-        tmem_ld32(lane_base + A3_OCOL + cb * 32, o);
+        const int col0 = half ? C0 : 0;
+        tmem_ld32(lane_base + A3_OCOL + col0, o);
         ptx::tmem_ld_wait();
+        const int nvec = half ? (HD - C0) / 8 : 4;  // 16-byte chunks out of these 32 columns
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          uint4 v;
-          v.x = pack_bf16x2(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
-          v.y = pack_bf16x2(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
-          v.z = pack_bf16x2(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
-          v.w = pack_bf16x2(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
-          *reinterpret_cast<uint4*>(stg + (((uint32_t)(cb * 4 + q) ^ swz) << 4)) = v;
+          if (q < nvec) {
+            uint4 v;
+            v.x = pack_bf16x2(__uint_as_float(o[8 * q]) * inv, __uint_as_float(o[8 * q + 1]) * inv);
+            v.y = pack_bf16x2(__uint_as_float(o[8 * q + 2]) * inv, __uint_as_float(o[8 * q + 3]) * inv);
+            v.z = pack_bf16x2(__uint_as_float(o[8 * q + 4]) * inv, __uint_as_float(o[8 * q + 5]) * inv);
+            v.w = pack_bf16x2(__uint_as_float(o[8 * q + 6]) * inv, __uint_as_float(o[8 * q + 7]) * inv);
+            *reinterpret_cast<uint4*>(stg + ((((uint32_t)(col0 >> 3) + q) ^ swz) << 4)) = v;
+          }
         }
-      }
-      if (HD == 72) {  // columns [64, 72)
-        uint32_t o2[16];
-        ptx::tmem_ld16(lane_base + A3_OCOL + 64, o2);
-        ptx::tmem_ld_wait();
-        uint4 v;
-        v.x = pack_bf16x2(__uint_as_float(o2[0]) * inv, __uint_as_float(o2[1]) * inv);
-        v.y = pack_bf16x2(__uint_as_float(o2[2]) * inv, __uint_as_float(o2[3]) * inv);
-        v.z = pack_bf16x2(__uint_as_float(o2[4]) * inv, __uint_as_float(o2[5]) * inv);
-        v.w = pack_bf16x2(__uint_as_float(o2[6]) * inv, __uint_as_float(o2[7]) * inv);
-        *reinterpret_cast<uint4*>(stg + (8 << 4)) = v;
+        if (HD == 72 && half == 0) {  // columns [32, 48)
+          uint32_t o2[16];
+          ptx::tmem_ld16(lane_base + A3_OCOL + 32, o2);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            uint4 v;
+            v.x = pack_bf16x2(__uint_as_float(o2[8 * q]) * inv, __uint_as_float(o2[8 * q + 1]) * inv);
+            v.y = pack_bf16x2(__uint_as_float(o2[8 * q + 2]) * inv, __uint_as_float(o2[8 * q + 3]) * inv);
+            v.z = pack_bf16x2(__uint_as_float(o2[8 * q + 4]) * inv, __uint_as_float(o2[8 * q + 5]) * inv);
+            v.w = pack_bf16x2(__uint_as_float(o2[8 * q + 6]) * inv, __uint_as_float(o2[8 * q + 7]) * inv);
+            *reinterpret_cast<uint4*>(stg + ((4 + q) << 4)) = v;
+          }
+        }
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(t_empty(g));  // O free for P_0 V_0 of this group's next unit
-      if (lse && q0 + row < Tn)
-        lse[((size_t)r * h + head) * Tn + q0 + row] = l_run > 0.f ? (m_run * sl2 + log2f(l_run)) * 0.6931471805599453f : 0.f;
+      if (lse && half == 0 && q0 + row < Tn)
+        lse[((size_t)r * h + head) * Tn + q0 + row] = l > 0.f ? (m_run * sl2 + log2f(l)) * 0.6931471805599453f : 0.f;
       ptx::fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        a3_tma_store_3d(&tmOut, sQ + g * BLOCK + quarter * 32 * C::OUT_ROW, head * HD, q0 + quarter * 32, r);
+      ptx::named_bar_sync(bar_id, A3_GROUP);
+      if (gt == 0) {
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) a3_tma_store_3d(&tmOut, sQ + g * BLOCK + qq * 32 * C::OUT_ROW, head * HD, q0 + qq * 32, r);
         ptx::tma_store_commit();
-        ptx::tma_store_wait_read<0>();       // the staging is the group's only Q buffer: release it as soon as the store has read it
+        ptx::tma_store_wait_read<0>();       // the staging is the group's only Q buffer: release it as soon as the stores have read it
         ptx::mbar_arrive(q_empty(g));
       }
       ++ucnt;
     }
-    if (lane == 0) ptx::tma_store_wait_all();
+    if (gt == 0) ptx::tma_store_wait_all();
   }
   ptx::tc_fence_before();
   __syncthreads();
