@@ -3,9 +3,11 @@
 // FITB200_EPI_BIAS_ROPE).  Same arithmetic as Attention.forward (fit.py:176-188; head merge fit.py:220-227) with the softmax
 // evaluated block by block over the keys (running row max / row sum, O rescaled when the max moves), the schedule of attn_tc2.cu
 // (persistent CTAs, event-driven MMA issuer, row-per-thread softmax groups) extended by a key loop:
-//   warps 0, 1  TMA producers of group 0 / 1: per 128-query unit Q once, then K_j / V_j blocks of 128 keys through a 2-stage ring
+//   warp 0      TMA producer: per PAIR of 128-query tiles of one (sample, head) item Q0 / Q1 once, then K_j / V_j blocks of 128 keys
+//               through ONE 4-stage ring that both tiles multiply against (half the L2 -> SM traffic of a ring per tile; the first
+//               blocks of the next pair are prefetched before its Q tiles, which wait for the previous epilogue)
 //   warp 2      MMA issuer for both groups: S_j = Q K_j^T (TMEM region g, columns [0, 128)), then O += P_j V_j (columns [128, 128+DP))
-//   warps 4-11  softmax / epilogue group 0, warps 12-19 group 1: each group owns one unit at a time; two threads per query row
+//   warps 4-11  softmax / epilogue group 0 (first tile of the pair), warps 12-19 group 1 (second tile); two threads per query row
 //               (TMEM lane quarter = warp & 3, key half = 64 of the block's 128 keys): block max (halves exchanged through shared
 //               memory, one named barrier per block), P_j = exp2(S_j - max) as bf16 written over the first 32 of the thread's own 64
 //               score columns (keys [0,64) -> columns [0,32), keys [64,128) -> columns [64,96)), partial row sums joined at the end,
@@ -30,7 +32,7 @@ constexpr int A3_GROUP = 256;                     // threads of one softmax grou
 constexpr int A3_THREADS = 128 + 2 * A3_GROUP;    // warps 0-1 producers, 2 MMA, 3 spare, 4-11 group 0, 12-19 group 1
 constexpr int A3_OCOL = 128;                      // O accumulator columns inside a group's TMEM region
 constexpr float A3_TAU = 8.f;                      // log2 of the growth of the row maximum that triggers a rescale of O
-constexpr int A3_NS = 2;                          // K / V ring stages per group
+constexpr int A3_NS = 4;                          // K / V ring stages (one ring, read by both groups)
 
 __device__ __forceinline__ void a3_tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];\n" ::"l"(reinterpret_cast<uint64_t>(m)),
@@ -45,25 +47,30 @@ struct A3Cfg {
   static constexpr int CS = 128 * 16;                  // chunk-column stride inside a 128-row block
   static constexpr int BLOCK = CHP * CS;               // bytes of one 128-row operand block (incl. the contraction pad chunk)
   static constexpr int Q_OFF = 0;                      // [2 groups]
-  static constexpr int KV_OFF = 2 * BLOCK;             // [2 groups][A3_NS][K, V]
-  static constexpr int BAR_OFF = KV_OFF + 2 * A3_NS * 2 * BLOCK;
-  static constexpr int NBARS_G = 2 + 4 * A3_NS + 4;    // q_full q_empty | k_full v_full k_empty v_empty [NS] | s_full p_ready o_full t_empty
-  static constexpr int SCR_OFF = BAR_OFF + 2 * NBARS_G * 8 + 16;   // per group: block max [2 parities][2 halves][128] + row sum [2][128]
+  static constexpr int KV_OFF = 2 * BLOCK;             // [A3_NS][K, V]
+  static constexpr int BAR_OFF = KV_OFF + A3_NS * 2 * BLOCK;
+  static constexpr int NBARS_G = 6;                    // per group: q_full q_empty s_full p_ready o_full t_empty
+  static constexpr int NBARS = 2 * NBARS_G + 4 * A3_NS;   // + ring: k_full v_full k_empty v_empty [NS]
+  static constexpr int SCR_OFF = BAR_OFF + NBARS * 8 + 16;   // per group: block max [2 parities][2 halves][128] + row sum [2][128]
   static constexpr int SCR_BYTES = 6 * 128 * 4;
   static constexpr int SMEM = SCR_OFF + 2 * SCR_BYTES + 1024 /*alignment slack*/;
   static constexpr int OUT_ROW = HD * 2;               // staging row bytes (dense TMA box)
 };
 
-struct A3Unit { int r, head, q0, kvl, nkb; };
+// A pair = two consecutive 128-query tiles of one (sample, head) item: tile 0 goes to softmax group 0, tile 1 to group 1, and both
+// multiply against the SAME K_j / V_j blocks in shared memory (half the L2 -> SM traffic of one ring per group).
+struct A3Unit { int r, head, q0, kvl, nkb; bool live0, live1; };
 
-// unit u = (item, query tile): item = (sample, head).  Returns false for padded query tiles (no tensor work, zero rows).
-__device__ __forceinline__ bool a3_decode(int u, int nq, int h, int Tn, const int32_t* __restrict__ kv_len, A3Unit& o) {
-  const int item = u / nq, qt = u - item * nq;
+// Returns false for pairs whose first tile is padding (no tensor work, zero rows).
+__device__ __forceinline__ bool a3_decode(int p, int npair, int h, int Tn, const int32_t* __restrict__ kv_len, A3Unit& o) {
+  const int item = p / npair, pi = p - item * npair;
   o.r = item / h; o.head = item - o.r * h;
   o.kvl = min(kv_len[o.r], Tn);
-  o.q0 = qt * A3_BQ;
+  o.q0 = pi * 2 * A3_BQ;
   o.nkb = (o.kvl + A3_BK - 1) / A3_BK;
-  return o.q0 < o.kvl;
+  o.live0 = o.q0 < o.kvl;
+  o.live1 = o.q0 + A3_BQ < o.kvl;
+  return o.live0;
 }
 
 template <int HD>
@@ -77,24 +84,23 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint8_t* sQ = sm + C::Q_OFF;
   uint8_t* sKV = sm + C::KV_OFF;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sm + C::BAR_OFF);
-  // barrier g-th group: base = bars + g * NB
   auto q_full = [&](int g) { return bars + g * NB; };
   auto q_empty = [&](int g) { return bars + g * NB + 1; };
-  auto k_full = [&](int g, int s) { return bars + g * NB + 2 + s; };
-  auto v_full = [&](int g, int s) { return bars + g * NB + 2 + A3_NS + s; };
-  auto k_empty = [&](int g, int s) { return bars + g * NB + 2 + 2 * A3_NS + s; };
-  auto v_empty = [&](int g, int s) { return bars + g * NB + 2 + 3 * A3_NS + s; };
-  auto s_full = [&](int g) { return bars + g * NB + 2 + 4 * A3_NS; };
-  auto p_ready = [&](int g) { return bars + g * NB + 3 + 4 * A3_NS; };
-  auto o_full = [&](int g) { return bars + g * NB + 4 + 4 * A3_NS; };
-  auto t_empty = [&](int g) { return bars + g * NB + 5 + 4 * A3_NS; };
-  auto kbuf = [&](int g, int s) { return sKV + ((g * A3_NS + s) * 2) * BLOCK; };
-  auto vbuf = [&](int g, int s) { return sKV + ((g * A3_NS + s) * 2 + 1) * BLOCK; };
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NB);
+  auto s_full = [&](int g) { return bars + g * NB + 2; };
+  auto p_ready = [&](int g) { return bars + g * NB + 3; };
+  auto o_full = [&](int g) { return bars + g * NB + 4; };
+  auto t_empty = [&](int g) { return bars + g * NB + 5; };
+  auto k_full = [&](int s) { return bars + 2 * NB + s; };
+  auto v_full = [&](int s) { return bars + 2 * NB + A3_NS + s; };
+  auto k_empty = [&](int s) { return bars + 2 * NB + 2 * A3_NS + s; };
+  auto v_empty = [&](int s) { return bars + 2 * NB + 3 * A3_NS + s; };
+  auto kbuf = [&](int s) { return sKV + (s * 2) * BLOCK; };
+  auto vbuf = [&](int s) { return sKV + (s * 2 + 1) * BLOCK; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + C::NBARS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nq = (Tn + A3_BQ - 1) / A3_BQ;  // query units per item
-  const int U = R * h * nq;
+  const int npair = (Tn + 2 * A3_BQ - 1) / (2 * A3_BQ);  // query-tile pairs per item
+  const int NP = R * h * npair;
   const int D = h * HD;
 
   if (tid == 0) {
@@ -102,17 +108,17 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     ptx::prefetch_tmap(&tmOut);
     for (int g = 0; g < 2; ++g) {
       ptx::mbar_init(q_full(g), 1); ptx::mbar_init(q_empty(g), 1);
-      for (int s = 0; s < A3_NS; ++s) {
-        ptx::mbar_init(k_full(g, s), 1); ptx::mbar_init(v_full(g, s), 1); ptx::mbar_init(k_empty(g, s), 1); ptx::mbar_init(v_empty(g, s), 1);
-      }
       ptx::mbar_init(s_full(g), 1); ptx::mbar_init(p_ready(g), A3_GROUP); ptx::mbar_init(o_full(g), 1); ptx::mbar_init(t_empty(g), A3_GROUP);
+    }
+    for (int s = 0; s < A3_NS; ++s) {
+      ptx::mbar_init(k_full(s), 1); ptx::mbar_init(v_full(s), 1); ptx::mbar_init(k_empty(s), 1); ptx::mbar_init(v_empty(s), 1);
     }
     ptx::fence_mbar_init();
   }
   if (DP != HD) {  // contraction padding (head_dim 72 -> 80) of every Q / K block: zeroed once, TMA boxes never touch it
-    for (int i = tid; i < (2 + 2 * A3_NS) * 128; i += A3_THREADS) {
+    for (int i = tid; i < (2 + A3_NS) * 128; i += A3_THREADS) {
       const int b = i >> 7, rr = i & 127;
-      uint8_t* blk = b < 2 ? sQ + b * BLOCK : kbuf((b - 2) / A3_NS, (b - 2) % A3_NS);
+      uint8_t* blk = b < 2 ? sQ + b * BLOCK : kbuf(b - 2);
       *reinterpret_cast<uint4*>(blk + CH * CS + rr * 16) = make_uint4(0, 0, 0, 0);
     }
   }
@@ -124,43 +130,62 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   const uint32_t tb = *tmem_slot;
   constexpr uint32_t BOX = CH * CS;  // bytes of one TMA box {8, 128, CH}
 
-  if (warp < 2) {
-    // ------------------------------------------------------------------------------------------ TMA producer of group `warp`
+  if (warp == 0) {
+    // ------------------------------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      const int g = warp;
-      int ucnt = 0, bcnt = 0;
-      for (int u = blockIdx.x + g * gridDim.x; u < U; u += 2 * gridDim.x) {
-        A3Unit un;
-        if (!a3_decode(u, nq, h, Tn, kv_len, un)) continue;
-        const int row0 = un.r * Tn, cq = un.head * CH, ck = (D + un.head * HD) / 8, cv = (2 * D + un.head * HD) / 8;
-        ptx::mbar_wait_sleep(q_empty(g), (ucnt & 1) ^ 1, 64);
-        ptx::mbar_arrive_expect_tx(q_full(g), BOX);
-        tma_load_3d(sQ + g * BLOCK, &tmQKV, q_full(g), 0, row0 + un.q0, cq);
-        for (int j = 0; j < un.nkb; ++j, ++bcnt) {
-          const int slot = bcnt % A3_NS; const uint32_t ph = (bcnt / A3_NS) & 1;
-          ptx::mbar_wait_sleep(k_empty(g, slot), ph ^ 1, 64);
-          ptx::mbar_arrive_expect_tx(k_full(g, slot), BOX);
-          tma_load_3d(kbuf(g, slot), &tmQKV, k_full(g, slot), 0, row0 + j * A3_BK, ck);
-          ptx::mbar_wait_sleep(v_empty(g, slot), ph ^ 1, 64);
-          ptx::mbar_arrive_expect_tx(v_full(g, slot), BOX);
-          tma_load_3d(vbuf(g, slot), &tmQKV, v_full(g, slot), 0, row0 + j * A3_BK, cv);
+      int uc0 = 0, uc1 = 0, bseq = 0;
+      for (int p = blockIdx.x; p < NP; p += gridDim.x) {
+        A3Unit pr;
+        if (!a3_decode(p, npair, h, Tn, kv_len, pr)) continue;
+        const int row0 = pr.r * Tn, cq = pr.head * CH, ck = (D + pr.head * HD) / 8, cv = (2 * D + pr.head * HD) / 8;
+        auto load_kv = [&](int j) {
+          const int slot = bseq % A3_NS; const uint32_t ph = (bseq / A3_NS) & 1;
+          ptx::mbar_wait_sleep(k_empty(slot), ph ^ 1, 64);
+          ptx::mbar_arrive_expect_tx(k_full(slot), BOX);
+          tma_load_3d(kbuf(slot), &tmQKV, k_full(slot), 0, row0 + j * A3_BK, ck);
+          ptx::mbar_wait_sleep(v_empty(slot), ph ^ 1, 64);
+          ptx::mbar_arrive_expect_tx(v_full(slot), BOX);
+          tma_load_3d(vbuf(slot), &tmQKV, v_full(slot), 0, row0 + j * A3_BK, cv);
+          ++bseq;
+        };
+        // the first K / V blocks go out BEFORE the Q tiles: Q waits for the previous pair's epilogue (its buffer is the output
+        // staging), the ring does not
+        const int pre = min(2, pr.nkb);
+        for (int j = 0; j < pre; ++j) load_kv(j);
+        ptx::mbar_wait_sleep(q_empty(0), (uc0 & 1) ^ 1, 64);
+        ptx::mbar_arrive_expect_tx(q_full(0), BOX);
+        tma_load_3d(sQ, &tmQKV, q_full(0), 0, row0 + pr.q0, cq);
+        ++uc0;
+        if (pr.live1) {
+          ptx::mbar_wait_sleep(q_empty(1), (uc1 & 1) ^ 1, 64);
+          ptx::mbar_arrive_expect_tx(q_full(1), BOX);
+          tma_load_3d(sQ + BLOCK, &tmQKV, q_full(1), 0, row0 + pr.q0 + A3_BQ, cq);
+          ++uc1;
         }
-        ++ucnt;
+        for (int j = pre; j < pr.nkb; ++j) load_kv(j);
       }
     }
     __syncwarp();
   } else if (warp == 2) {
     // ------------------------------------------------------------------------------------------ MMA issuer (both groups)
     if (lane == 0) {
-      struct St { int u, nkb, kvl, j, stage, ucnt, bcnt; bool active; } st[2];
+      // group state: current pair, block j, stage (0 = S_j pending, 1 = P_j V_j pending), ucnt = units done (q / o / t phases),
+      // bc = blocks done by THIS group (s_full / p_ready phases), bseq = ring sequence number of its current block
+      struct St { int p, nkb, kvl, need, j, stage, ucnt, bc, bseq; bool active; } st[2];
       auto next_unit = [&](St& s, int g, int from) {
         s.active = false;
-        for (int u = from; u < U; u += 2 * gridDim.x) {
-          A3Unit un;
-          if (a3_decode(u, nq, h, Tn, kv_len, un)) { s.u = u; s.nkb = un.nkb; s.kvl = un.kvl; s.j = 0; s.stage = 0; s.active = true; break; }
+        for (int p = from; p < NP; p += gridDim.x) {
+          A3Unit pr;
+          if (!a3_decode(p, npair, h, Tn, kv_len, pr)) continue;
+          if (g == 1 && !pr.live1) { s.bseq += pr.nkb; continue; }   // group 0 alone walks this pair's blocks
+          s.p = p; s.nkb = pr.nkb; s.kvl = pr.kvl; s.need = pr.live1 ? 2 : 1; s.j = 0; s.stage = 0; s.active = true;
+          break;
         }
       };
-      for (int g = 0; g < 2; ++g) { st[g].ucnt = 0; st[g].bcnt = 0; next_unit(st[g], g, blockIdx.x + g * gridDim.x); }
+      int cnt_s[A3_NS], cnt_pv[A3_NS];
+#pragma unroll
+      for (int i = 0; i < A3_NS; ++i) cnt_s[i] = cnt_pv[i] = 0;
+      for (int g = 0; g < 2; ++g) { st[g].ucnt = 0; st[g].bc = 0; st[g].bseq = 0; next_unit(st[g], g, blockIdx.x); }
       uint32_t spins = 0;
       while (st[0].active || st[1].active) {
         bool progressed = false;
@@ -170,26 +195,26 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           if (!s.active) continue;
           const uint32_t tr = tb + g * 256;
           if (s.stage == 1) {
-            const int slot = s.bcnt % A3_NS; const uint32_t ph = (s.bcnt / A3_NS) & 1;
+            const int slot = s.bseq % A3_NS; const uint32_t ph = (s.bseq / A3_NS) & 1;
             const int nk16 = (min(A3_BK, s.kvl - s.j * A3_BK) + 15) & ~15;
             // P_0 V_0 overwrites O: the previous unit's epilogue must have read it (t_empty)
-            if ((s.j > 0 || ptx::mbar_try_wait(t_empty(g), (s.ucnt & 1) ^ 1)) && ptx::mbar_try_wait(p_ready(g), s.bcnt & 1) &&
-                ptx::mbar_try_wait(v_full(g, slot), ph)) {
+            if ((s.j > 0 || ptx::mbar_try_wait(t_empty(g), (s.ucnt & 1) ^ 1)) && ptx::mbar_try_wait(p_ready(g), s.bc & 1) &&
+                ptx::mbar_try_wait(v_full(slot), ph)) {
               ptx::tc_fence_after();
               const uint32_t idesc = ptx::idesc_bf16_f32(A3_BQ, DP) | (1u << 16);  // B (= V) is MN-major
               const int ksteps = nk16 >> 4;
-              const uint8_t* v0 = vbuf(g, slot);
+              const uint8_t* v0 = vbuf(slot);
               for (int k = 0; k < ksteps; ++k) {
                 const uint64_t db = desc_nosw(ptx::smem_u32(v0 + k * 256), 128, CS);
                 // P of keys [0, 64) sits in columns [0, 32), P of keys [64, 128) in columns [64, 96) (each key half over its own scores)
                 mma_f16_ts(tr + A3_OCOL, tr + (k < 4 ? 8 * k : 64 + 8 * (k - 4)), db, idesc, (s.j > 0 || k > 0) ? 1u : 0u);
               }
-              ptx::mma_commit(v_empty(g, slot));
-              ++s.bcnt;
+              if (++cnt_pv[slot] == s.need) { ptx::mma_commit(v_empty(slot)); cnt_pv[slot] = 0; }   // both groups' P_j V_j are out
+              ++s.bc; ++s.bseq;
               if (++s.j == s.nkb) {
                 ptx::mma_commit(o_full(g));
                 ++s.ucnt;
-                next_unit(s, g, s.u + 2 * gridDim.x);
+                next_unit(s, g, s.p + gridDim.x);
               } else {
                 s.stage = 0;
               }
@@ -200,19 +225,19 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           // softmax first gets its next scores first, which keeps the two groups in anti-phase -- one multiplies while the other
           // exponentiates.  Serving the groups strictly in turn interleaved PV(g1) PV(g0) S(g1) S(g0) and locked them in step.
           if (s.active && s.stage == 0) {
-            const int slot = s.bcnt % A3_NS; const uint32_t ph = (s.bcnt / A3_NS) & 1;
+            const int slot = s.bseq % A3_NS; const uint32_t ph = (s.bseq / A3_NS) & 1;
             const int nk16 = (min(A3_BK, s.kvl - s.j * A3_BK) + 15) & ~15;
-            if ((s.j > 0 || ptx::mbar_try_wait(q_full(g), s.ucnt & 1)) && ptx::mbar_try_wait(k_full(g, slot), ph)) {
+            if ((s.j > 0 || ptx::mbar_try_wait(q_full(g), s.ucnt & 1)) && ptx::mbar_try_wait(k_full(slot), ph)) {
               ptx::tc_fence_after();
               const uint32_t idesc = ptx::idesc_bf16_f32(A3_BQ, nk16);
 #pragma unroll
               for (int k = 0; k < DP / 16; ++k) {
                 const uint64_t da = desc_nosw(ptx::smem_u32(sQ + g * BLOCK + 2 * k * CS), CS, 128);
-                const uint64_t db = desc_nosw(ptx::smem_u32(kbuf(g, slot) + 2 * k * CS), CS, 128);
+                const uint64_t db = desc_nosw(ptx::smem_u32(kbuf(slot) + 2 * k * CS), CS, 128);
                 ptx::mma_f16_ss(tr, da, db, idesc, k != 0);
               }
               ptx::mma_commit(s_full(g));
-              ptx::mma_commit(k_empty(g, slot));
+              if (++cnt_s[slot] == s.need) { ptx::mma_commit(k_empty(slot)); cnt_s[slot] = 0; }   // both groups' S_j are out
               s.stage = 1;
               progressed = true;
             }
@@ -237,10 +262,11 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const float sl2 = rsqrtf((float)HD) * 1.4426950408889634f;  // softmax scale folded with log2(e)
     const int bar_id = 1 + g;
     int ucnt = 0, bcnt = 0;
-    for (int u = blockIdx.x + g * gridDim.x; u < U; u += 2 * gridDim.x) {
+    for (int p = blockIdx.x; p < NP; p += gridDim.x) {
       A3Unit un;
-      const bool live = a3_decode(u, nq, h, Tn, kv_len, un);
-      const int r = un.r, head = un.head, q0 = un.q0;
+      a3_decode(p, npair, h, Tn, kv_len, un);
+      const bool live = g ? un.live1 : un.live0;
+      const int r = un.r, head = un.head, q0 = un.q0 + g * A3_BQ;
       if (!live) {  // padded query tile: zero output rows, no tensor work
         for (int i = gt; i < A3_BQ * CH; i += A3_GROUP) {
           const int rw = i / CH, c = i - rw * CH;
@@ -443,9 +469,9 @@ static int launch_attn_tc3(const void* qkv, const int32_t* kv_len, const uint8_t
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (rc != CUDA_SUCCESS) { set_last_error("attn_tc3: cuTensorMapEncodeTiled (out) failed (%d)", (int)rc); return FITB200_ERR_CUDA; }
   }
-  const int nq = (Tn + A3_BQ - 1) / A3_BQ;
-  const long units = (long)R * h * nq;
-  const int grid = units < sm_count() ? (int)units : sm_count();
+  const int npair = (Tn + 2 * A3_BQ - 1) / (2 * A3_BQ);
+  const long pairs = (long)R * h * npair;
+  const int grid = pairs < sm_count() ? (int)pairs : sm_count();
   attn_tc3_kernel<HD><<<grid, A3_THREADS, C::SMEM, s>>>(tmQ, tmO, kv_len, mask, R, Tn, h, (__nv_bfloat16*)out, lse);
   FITB200_CHECK_LAUNCH("attn_tc3");
   return FITB200_OK;
