@@ -32,7 +32,8 @@ constexpr int A3_GROUP = 256;                     // threads of one softmax grou
 constexpr int A3_THREADS = 128 + 2 * A3_GROUP;    // warps 0-1 producers, 2 MMA, 3 spare, 4-11 group 0, 12-19 group 1
 constexpr int A3_OCOL = 128;                      // O accumulator columns inside a group's TMEM region
 constexpr float A3_TAU = 8.f;                      // log2 of the growth of the row maximum that triggers a rescale of O
-constexpr int A3_NS = 4;                          // K / V ring stages (one ring, read by both groups)
+constexpr int A3_NS = 3;                          // K / V ring stages (one ring, read by both groups)
+constexpr int A3_NQB = 2;                         // Q buffers per group (the next unit's Q lands while this one computes / stores)
 
 __device__ __forceinline__ void a3_tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];\n" ::"l"(reinterpret_cast<uint64_t>(m)),
@@ -46,10 +47,10 @@ struct A3Cfg {
   static constexpr int CHP = DP / 8, CH = HD / 8;
   static constexpr int CS = 128 * 16;                  // chunk-column stride inside a 128-row block
   static constexpr int BLOCK = CHP * CS;               // bytes of one 128-row operand block (incl. the contraction pad chunk)
-  static constexpr int Q_OFF = 0;                      // [2 groups]
-  static constexpr int KV_OFF = 2 * BLOCK;             // [A3_NS][K, V]
+  static constexpr int Q_OFF = 0;                      // [2 groups][A3_NQB]
+  static constexpr int KV_OFF = 2 * A3_NQB * BLOCK;    // [A3_NS][K, V]
   static constexpr int BAR_OFF = KV_OFF + A3_NS * 2 * BLOCK;
-  static constexpr int NBARS_G = 6;                    // per group: q_full q_empty s_full p_ready o_full t_empty
+  static constexpr int NBARS_G = 4 + 2 * A3_NQB;       // per group: s_full p_ready o_full t_empty | q_full q_empty [NQB]
   static constexpr int NBARS = 2 * NBARS_G + 4 * A3_NS;   // + ring: k_full v_full k_empty v_empty [NS]
   static constexpr int SCR_OFF = BAR_OFF + NBARS * 8 + 16;   // per group: block max [2 parities][2 halves][128] + row sum [2][128]
   static constexpr int SCR_BYTES = 6 * 128 * 4;
@@ -84,12 +85,13 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint8_t* sQ = sm + C::Q_OFF;
   uint8_t* sKV = sm + C::KV_OFF;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sm + C::BAR_OFF);
-  auto q_full = [&](int g) { return bars + g * NB; };
-  auto q_empty = [&](int g) { return bars + g * NB + 1; };
-  auto s_full = [&](int g) { return bars + g * NB + 2; };
-  auto p_ready = [&](int g) { return bars + g * NB + 3; };
-  auto o_full = [&](int g) { return bars + g * NB + 4; };
-  auto t_empty = [&](int g) { return bars + g * NB + 5; };
+  auto s_full = [&](int g) { return bars + g * NB; };
+  auto p_ready = [&](int g) { return bars + g * NB + 1; };
+  auto o_full = [&](int g) { return bars + g * NB + 2; };
+  auto t_empty = [&](int g) { return bars + g * NB + 3; };
+  auto q_full = [&](int g, int b) { return bars + g * NB + 4 + b; };
+  auto q_empty = [&](int g, int b) { return bars + g * NB + 4 + A3_NQB + b; };
+  auto qbuf = [&](int g, int b) { return sQ + (g * A3_NQB + b) * BLOCK; };
   auto k_full = [&](int s) { return bars + 2 * NB + s; };
   auto v_full = [&](int s) { return bars + 2 * NB + A3_NS + s; };
   auto k_empty = [&](int s) { return bars + 2 * NB + 2 * A3_NS + s; };
@@ -107,7 +109,7 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     ptx::prefetch_tmap(&tmQKV);
     ptx::prefetch_tmap(&tmOut);
     for (int g = 0; g < 2; ++g) {
-      ptx::mbar_init(q_full(g), 1); ptx::mbar_init(q_empty(g), 1);
+      for (int b = 0; b < A3_NQB; ++b) { ptx::mbar_init(q_full(g, b), 1); ptx::mbar_init(q_empty(g, b), 1); }
       ptx::mbar_init(s_full(g), 1); ptx::mbar_init(p_ready(g), A3_GROUP); ptx::mbar_init(o_full(g), 1); ptx::mbar_init(t_empty(g), A3_GROUP);
     }
     for (int s = 0; s < A3_NS; ++s) {
@@ -116,9 +118,9 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     ptx::fence_mbar_init();
   }
   if (DP != HD) {  // contraction padding (head_dim 72 -> 80) of every Q / K block: zeroed once, TMA boxes never touch it
-    for (int i = tid; i < (2 + A3_NS) * 128; i += A3_THREADS) {
+    for (int i = tid; i < (2 * A3_NQB + A3_NS) * 128; i += A3_THREADS) {
       const int b = i >> 7, rr = i & 127;
-      uint8_t* blk = b < 2 ? sQ + b * BLOCK : kbuf(b - 2);
+      uint8_t* blk = b < 2 * A3_NQB ? sQ + b * BLOCK : kbuf(b - 2 * A3_NQB);
       *reinterpret_cast<uint4*>(blk + CH * CS + rr * 16) = make_uint4(0, 0, 0, 0);
     }
   }
@@ -148,21 +150,18 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           tma_load_3d(vbuf(slot), &tmQKV, v_full(slot), 0, row0 + j * A3_BK, cv);
           ++bseq;
         };
-        // the first K / V blocks go out BEFORE the Q tiles: Q waits for the previous pair's epilogue (its buffer is the output
-        // staging), the ring does not
-        const int pre = min(2, pr.nkb);
-        for (int j = 0; j < pre; ++j) load_kv(j);
-        ptx::mbar_wait_sleep(q_empty(0), (uc0 & 1) ^ 1, 64);
-        ptx::mbar_arrive_expect_tx(q_full(0), BOX);
-        tma_load_3d(sQ, &tmQKV, q_full(0), 0, row0 + pr.q0, cq);
+        // Q tiles first: their buffers were released two units ago (double buffered), so these waits do not hold up the ring
+        ptx::mbar_wait_sleep(q_empty(0, uc0 % A3_NQB), ((uc0 / A3_NQB) & 1) ^ 1, 64);
+        ptx::mbar_arrive_expect_tx(q_full(0, uc0 % A3_NQB), BOX);
+        tma_load_3d(qbuf(0, uc0 % A3_NQB), &tmQKV, q_full(0, uc0 % A3_NQB), 0, row0 + pr.q0, cq);
         ++uc0;
         if (pr.live1) {
-          ptx::mbar_wait_sleep(q_empty(1), (uc1 & 1) ^ 1, 64);
-          ptx::mbar_arrive_expect_tx(q_full(1), BOX);
-          tma_load_3d(sQ + BLOCK, &tmQKV, q_full(1), 0, row0 + pr.q0 + A3_BQ, cq);
+          ptx::mbar_wait_sleep(q_empty(1, uc1 % A3_NQB), ((uc1 / A3_NQB) & 1) ^ 1, 64);
+          ptx::mbar_arrive_expect_tx(q_full(1, uc1 % A3_NQB), BOX);
+          tma_load_3d(qbuf(1, uc1 % A3_NQB), &tmQKV, q_full(1, uc1 % A3_NQB), 0, row0 + pr.q0 + A3_BQ, cq);
           ++uc1;
         }
-        for (int j = pre; j < pr.nkb; ++j) load_kv(j);
+        for (int j = 0; j < pr.nkb; ++j) load_kv(j);
       }
     }
     __syncwarp();
@@ -227,12 +226,13 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           if (s.active && s.stage == 0) {
             const int slot = s.bseq % A3_NS; const uint32_t ph = (s.bseq / A3_NS) & 1;
             const int nk16 = (min(A3_BK, s.kvl - s.j * A3_BK) + 15) & ~15;
-            if ((s.j > 0 || ptx::mbar_try_wait(q_full(g), s.ucnt & 1)) && ptx::mbar_try_wait(k_full(slot), ph)) {
+            const int qb = s.ucnt % A3_NQB;
+            if ((s.j > 0 || ptx::mbar_try_wait(q_full(g, qb), (s.ucnt / A3_NQB) & 1)) && ptx::mbar_try_wait(k_full(slot), ph)) {
               ptx::tc_fence_after();
               const uint32_t idesc = ptx::idesc_bf16_f32(A3_BQ, nk16);
 #pragma unroll
               for (int k = 0; k < DP / 16; ++k) {
-                const uint64_t da = desc_nosw(ptx::smem_u32(sQ + g * BLOCK + 2 * k * CS), CS, 128);
+                const uint64_t da = desc_nosw(ptx::smem_u32(qbuf(g, qb) + 2 * k * CS), CS, 128);
                 const uint64_t db = desc_nosw(ptx::smem_u32(kbuf(slot) + 2 * k * CS), CS, 128);
                 ptx::mma_f16_ss(tr, da, db, idesc, k != 0);
               }
@@ -385,7 +385,7 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       const float l = ssum[row] + ssum[A3_BQ + row];
       const float inv = l > 0.f ? 1.f / l : 0.f;
       constexpr int C0 = HD == 64 ? 32 : 48;  // columns [0, C0) -> half 0, [C0, HD) -> half 1
-      uint8_t* stg = sQ + g * BLOCK + row * C::OUT_ROW;
+      uint8_t* stg = qbuf(g, ucnt % A3_NQB) + row * C::OUT_ROW;
       const uint32_t swz = HD == 64 ? (uint32_t)(row & 7) : 0u;  // 128-byte rows: 128B-swizzled box (conflict-free 16-byte stores)
       {
         uint32_t o[32];
@@ -427,10 +427,10 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       ptx::named_bar_sync(bar_id, A3_GROUP);
       if (gt == 0) {
 #pragma unroll
-        for (int qq = 0; qq < 4; ++qq) a3_tma_store_3d(&tmOut, sQ + g * BLOCK + qq * 32 * C::OUT_ROW, head * HD, q0 + qq * 32, r);
+        for (int qq = 0; qq < 4; ++qq) a3_tma_store_3d(&tmOut, qbuf(g, ucnt % A3_NQB) + qq * 32 * C::OUT_ROW, head * HD, q0 + qq * 32, r);
         ptx::tma_store_commit();
-        ptx::tma_store_wait_read<0>();       // the staging is the group's only Q buffer: release it as soon as the stores have read it
-        ptx::mbar_arrive(q_empty(g));
+        ptx::tma_store_wait_read<0>();       // release the staging (= this unit's Q buffer) as soon as the stores have read it:
+        ptx::mbar_arrive(q_empty(g, ucnt % A3_NQB));   // the Q tile of the unit after next lands while the next one computes
       }
       ++ucnt;
     }
