@@ -230,3 +230,26 @@ def test_headline_size_properties():
     assert torch.equal(torch.cat(parts), full)
     # the update actually moved the latents (a dead kernel would also be "shard invariant")
     assert float((full.cpu() - z).abs().mean()) > 1e-3
+
+
+@pytest.mark.parametrize("model_name,depth,hw", [("FiT-B/2", 2, (40, 40)), ("FiT-XL/2", 1, (40, 48)), ("FiT-B/2", 1, (64, 80))])
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16", 2e-2)])
+def test_resolution_extrapolation_forward_matches_oracle(model_name, depth, hw, precision, tol):
+    """BASELINE config 5, extrapolation leg: more than max_length = 256 tokens in one image (320x320 -> 400 tokens, 320x384 -> 480,
+    512x640 -> 1280) with the VisionNTK-scaled RoPE table (FiT/train.py:136-156).  The bf16 path runs the KV-blocked tcgen05
+    attention (attn_tc3.cu); compared with the CPU oracle on the same weights and inputs (the oracle itself is pinned to the reference
+    goldens at <= 256 tokens; the sequence length only changes the table and the attention span)."""
+    cfg = fo.model_config(model_name, depth=depth)
+    sd = fo.random_state_dict(cfg, seed=9)
+    h, w = hw
+    zz, tt, yy, pos, mask = synth.eval_batch(cfg, h, w, 256, seed=21, B=1)
+    assert pos.shape[1] == (h // 2) * (w // 2) > 256
+    with torch.no_grad():
+        want = fo.forward(sd, cfg, zz, tt, yy, pos, mask, train=False)
+        want_cfg = fo.forward_with_cfg(sd, cfg, zz, tt, yy, pos, mask, 1.5)
+    model = build_model(cfg, sd, precision)
+    with torch.no_grad():
+        got = model(zz.cuda(), tt.cuda(), yy.cuda(), pos.cuda(), mask.cuda(), train=False)
+        got_cfg = model.forward_with_cfg(zz.cuda(), tt.cuda(), yy.cuda(), pos.cuda(), mask.cuda(), 1.5)
+    assert rel_l2(got, want) < tol
+    assert rel_l2(got_cfg, want_cfg) < tol
