@@ -4,7 +4,7 @@
 // load -> S -> softmax -> PV -> store and relies on two resident CTAs for overlap (0.45-0.57 ms at R=512 XL/2, 10 us per tile, K / V
 // fetched once per query tile).  Here one CTA per SM walks (sample, head) items:
 //   warp 0      TMA producer: per item K (k_full) and V (v_full) once, per 128-query unit Q (q_full); rings: Q x3, K x2, V x2
-//   warp 1      MMA issuer: S(u) = Q K^T into TMEM region u&1, then P(u-1) V -> O(u-1): the softmax of unit u-1 overlaps S(u)
+//   warps 1, 2  MMA issuers, one per softmax group (its units only, blocking waits): S(u) = Q K^T into TMEM region u&1, then P(u) V -> O(u)
 //   warps 2-9   softmax / epilogue group 0 (units with even running index), warps 10-17 group 1 (odd): two-pass row-per-thread
 //               softmax on TMEM lanes, P back to TMEM as bf16, O normalised and staged in the unit's (already consumed) Q buffer,
 //               one TMA store per unit (3-D map, rows clipped at the sample's token count)
@@ -20,7 +20,7 @@ namespace fitb200 {
 
 constexpr int A2_BQ = 128;
 constexpr int A2_GROUP = 256;                    // threads of one softmax group (8 warps)
-constexpr int A2_THREADS = 64 + 2 * A2_GROUP;    // producer warp + MMA warp + two groups
+constexpr int A2_THREADS = 96 + 2 * A2_GROUP;    // producer warp + one MMA warp per group + two groups
 constexpr int A2_OCOL = 64;
 constexpr int A2_NQ = 3;                         // Q ring depth (units)
 
@@ -81,7 +81,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     ptx::prefetch_tmap(&tmOut);
     for (int i = 0; i < A2_NQ; ++i) { ptx::mbar_init(&q_full[i], 1); ptx::mbar_init(&q_empty[i], 1); }
     for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(&k_full[i], 1); ptx::mbar_init(&v_full[i], 1); ptx::mbar_init(&kv_empty[i], 1);
+      ptx::mbar_init(&k_full[i], 1); ptx::mbar_init(&v_full[i], 1); ptx::mbar_init(&kv_empty[i], 2);  // one arrival per MMA warp
       ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_ready[i], A2_GROUP); ptx::mbar_init(&o_full[i], 1); ptx::mbar_init(&t_empty[i], A2_GROUP);
     }
     ptx::fence_mbar_init();
@@ -132,27 +132,16 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------------------------------ MMA issuer
+  } else if (warp <= 2) {
+    // ------------------------------------------------------------------------------------------ MMA issuer of group warp - 1
+    // One issuing warp PER GROUP: a single thread serving both groups was the bottleneck of the kernel -- its ~500 instructions per
+    // unit pair (descriptor arithmetic, polling of six barriers) run at a fifth of an issue port it shares with four saturated
+    // softmax warps, so P V and S went out ~2000 clk after their barriers had flipped (clock64 trace, profiles/r1g_attn_tc3.txt).
+    // Each warp now walks only its own units with blocking waits, descriptors are advanced by constants, loops are unrolled.
     if (lane == 0) {
+      const int g = warp - 1;
+      const uint32_t tr = tb + g * 256;
       int uq = 0, ic = 0;
-      bool have_prev = false;
-      int p_g = 0, p_slot = 0, p_nk16 = 0, p_u = 0; uint32_t p_ph = 0; bool p_last = false;
-      auto pv_ready = [&]() { return ptx::mbar_try_wait(&p_ready[p_g], (p_u >> 1) & 1) && ptx::mbar_try_wait(&v_full[p_slot], p_ph); };
-      auto issue_pv = [&]() {
-        ptx::tc_fence_after();
-        const uint32_t tr = tb + p_g * 256;
-        const uint32_t idesc = ptx::idesc_bf16_f32(A2_BQ, DP) | (1u << 16);  // B (= V) is MN-major
-        const int ksteps = p_nk16 >> 4;
-        const uint8_t* v0 = sV + p_slot * 2 * BLOCK;
-        for (int k = 0; k < ksteps; ++k) {
-          const uint32_t a = tr + (k < 8 ? 8 * k : 192 + 8 * (k - 8));
-          const uint64_t db = desc_nosw(ptx::smem_u32(v0 + (k >> 3) * BLOCK + (k & 7) * 256), 128, CS);
-          mma_f16_ts(tr + A2_OCOL, a, db, idesc, k != 0);
-        }
-        ptx::mma_commit(&o_full[p_g]);
-        if (p_last) ptx::mma_commit(&kv_empty[p_slot]);  // K and V of the item are free once its last P V has retired
-      };
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int r = item / h;
         const int kvl = min(kv_len[r], Tn);
@@ -161,47 +150,53 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const int nk16 = (kvl + 15) & ~15, n0 = min(nk16, 128), n1 = nk16 - n0;
         const int slot = ic & 1; const uint32_t ph = (ic >> 1) & 1;
         for (int qt = 0; qt < nlive; ++qt, ++uq) {
-          const int g = uq & 1, qb = uq % A2_NQ;
-          // event driven: P V of the previous unit (other group) goes out as soon as its softmax is done, even while S of this
-          // unit still waits for ITS group to drain O of unit uq - 2 -- issuing strictly in order locked the two groups in step
-          bool pv_done = !have_prev;
-          uint32_t spins = 0;
-          for (;;) {
-            if (!pv_done && pv_ready()) { issue_pv(); pv_done = true; }
-            if (ptx::mbar_try_wait(&t_empty[g], ((uq >> 1) & 1) ^ 1) && ptx::mbar_try_wait(&q_full[qb], (uq / A2_NQ) & 1) &&
-                ptx::mbar_try_wait(&k_full[slot], ph))
-              break;
-            __nanosleep(32);  // the polling of this warp takes issue slots from the softmax warps of its scheduler
-            if (++spins > (1u << 24)) __trap();
-          }
+          if ((uq & 1) != g) continue;
+          const int qb = uq % A2_NQ;
+          ptx::mbar_wait(&t_empty[g], ((uq >> 1) & 1) ^ 1);
+          ptx::mbar_wait(&q_full[qb], (uq / A2_NQ) & 1);
+          ptx::mbar_wait(&k_full[slot], ph);
           ptx::tc_fence_after();
-          const uint32_t tr = tb + g * 256;
+          {
+            const uint64_t da0 = desc_nosw(ptx::smem_u32(sQ + qb * BLOCK), CS, 128);
+            const uint64_t db0 = desc_nosw(ptx::smem_u32(sK + slot * 2 * BLOCK), CS, 128);
+            constexpr uint64_t KSTEP = (2 * CS) >> 4, HALF = BLOCK >> 4;   // descriptor start-address field is in 16-byte units
+            const uint32_t id0 = ptx::idesc_bf16_f32(A2_BQ, n0);
 #pragma unroll
-          for (int hf = 0; hf < 2; ++hf) {
-            const int nn = hf ? n1 : n0;
-            if (nn > 0) {
-              const uint32_t idesc = ptx::idesc_bf16_f32(A2_BQ, nn);
+            for (int k = 0; k < DP / 16; ++k) ptx::mma_f16_ss(tr, da0 + k * KSTEP, db0 + k * KSTEP, id0, k != 0);
+            if (n1 > 0) {
+              const uint32_t id1 = ptx::idesc_bf16_f32(A2_BQ, n1);
 #pragma unroll
-              for (int k = 0; k < DP / 16; ++k) {
-                const uint64_t da = desc_nosw(ptx::smem_u32(sQ + qb * BLOCK + 2 * k * CS), CS, 128);
-                const uint64_t db = desc_nosw(ptx::smem_u32(sK + (slot * 2 + hf) * BLOCK + 2 * k * CS), CS, 128);
-                ptx::mma_f16_ss(tr + hf * 128, da, db, idesc, k != 0);
-              }
+              for (int k = 0; k < DP / 16; ++k) ptx::mma_f16_ss(tr + 128, da0 + k * KSTEP, db0 + HALF + k * KSTEP, id1, k != 0);
             }
           }
           ptx::mma_commit(&s_full[g]);
-          if (!pv_done) { while (!pv_ready()) { __nanosleep(32); if (++spins > (1u << 24)) __trap(); } issue_pv(); }
-          have_prev = true; p_g = g; p_slot = slot; p_nk16 = nk16; p_u = uq; p_ph = ph; p_last = qt == nlive - 1;
+          ptx::mbar_wait(&p_ready[g], (uq >> 1) & 1);
+          ptx::mbar_wait(&v_full[slot], ph);
+          ptx::tc_fence_after();
+          {
+            const uint32_t idesc = ptx::idesc_bf16_f32(A2_BQ, DP) | (1u << 16);  // B (= V) is MN-major
+            const int ksteps = nk16 >> 4;
+            const uint64_t dv0 = desc_nosw(ptx::smem_u32(sV + slot * 2 * BLOCK), 128, CS);
+            constexpr uint64_t HALF = BLOCK >> 4;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+              if (k < ksteps)
+                mma_f16_ts(tr + A2_OCOL, tr + (k < 8 ? 8 * k : 192 + 8 * (k - 8)), dv0 + (k >> 3) * HALF + (k & 7) * 16, idesc, k != 0);
+            }
+          }
+          ptx::mma_commit(&o_full[g]);
+          // K and V of the item are free once both groups' P V have retired (an item with one live unit arrives for both)
+          ptx::mma_commit(&kv_empty[slot]);
+          if (nlive == 1) ptx::mma_commit(&kv_empty[slot]);
         }
         ++ic;
       }
-      if (have_prev) { uint32_t spins = 0; while (!pv_ready()) { if (++spins > (1u << 24)) __trap(); } issue_pv(); }
     }
     __syncwarp();
   } else {
     // ------------------------------------------------------------------------------------------ softmax / epilogue groups
-    const int g = (warp - 2) >> 3;                 // group 0: warps 2-9, group 1: warps 10-17
-    const int gt = tid - 64 - g * A2_GROUP;        // thread inside the group
+    const int g = (warp - 3) >> 3;                 // group 0: warps 3-10, group 1: warps 11-18
+    const int gt = tid - 96 - g * A2_GROUP;        // thread inside the group
     const int gw = gt >> 5;                        // warp inside the group
     const int quarter = warp & 3, half = gw >> 2;  // TMEM lane quarter this warp may access; which half of the keys / columns
     const int row = quarter * 32 + lane;
