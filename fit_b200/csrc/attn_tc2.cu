@@ -5,7 +5,7 @@
 // fetched once per query tile).  Here one CTA per SM walks (sample, head) items:
 //   warp 0      TMA producer: per item K (k_full) and V (v_full) once, per 128-query unit Q (q_full); rings: Q x3, K x2, V x2
 //   warps 1, 2  MMA issuers, one per softmax group (its units only, blocking waits): S(u) = Q K^T into TMEM region u&1, then P(u) V -> O(u)
-//   warps 2-9   softmax / epilogue group 0 (units with even running index), warps 10-17 group 1 (odd): two-pass row-per-thread
+//   warps 3-10  softmax / epilogue group 0 (units with even running index), warps 11-18 group 1 (odd): two-pass row-per-thread
 //               softmax on TMEM lanes, P back to TMEM as bf16, O normalised and staged in the unit's (already consumed) Q buffer,
 //               one TMA store per unit (3-D map, rows clipped at the sample's token count)
 // TMEM: region g = columns [256 g, 256 g + 256): S in [0, n), P over [0, 64) and [192, 256), O in [64, 64 + DP)  (as attn_tc.cu).
