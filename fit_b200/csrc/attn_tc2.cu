@@ -141,55 +141,62 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     if (lane == 0) {
       const int g = warp - 1;
       const uint32_t tr = tb + g * 256;
-      int uq = 0, ic = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int r = item / h;
-        const int kvl = min(kv_len[r], Tn);
-        const int nlive = min(upi, (kvl + A2_BQ - 1) / A2_BQ);
-        if (nlive == 0) continue;
-        const int nk16 = (kvl + 15) & ~15, n0 = min(nk16, 128), n1 = nk16 - n0;
-        const int slot = ic & 1; const uint32_t ph = (ic >> 1) & 1;
-        for (int qt = 0; qt < nlive; ++qt, ++uq) {
-          if ((uq & 1) != g) continue;
-          const int qb = uq % A2_NQ;
-          ptx::mbar_wait(&t_empty[g], ((uq >> 1) & 1) ^ 1);
-          ptx::mbar_wait(&q_full[qb], (uq / A2_NQ) & 1);
-          ptx::mbar_wait(&k_full[slot], ph);
-          ptx::tc_fence_after();
-          {
-            const uint64_t da0 = desc_nosw(ptx::smem_u32(sQ + qb * BLOCK), CS, 128);
-            const uint64_t db0 = desc_nosw(ptx::smem_u32(sK + slot * 2 * BLOCK), CS, 128);
-            constexpr uint64_t KSTEP = (2 * CS) >> 4, HALF = BLOCK >> 4;   // descriptor start-address field is in 16-byte units
-            const uint32_t id0 = ptx::idesc_bf16_f32(A2_BQ, n0);
-#pragma unroll
-            for (int k = 0; k < DP / 16; ++k) ptx::mma_f16_ss(tr, da0 + k * KSTEP, db0 + k * KSTEP, id0, k != 0);
-            if (n1 > 0) {
-              const uint32_t id1 = ptx::idesc_bf16_f32(A2_BQ, n1);
-#pragma unroll
-              for (int k = 0; k < DP / 16; ++k) ptx::mma_f16_ss(tr + 128, da0 + k * KSTEP, db0 + HALF + k * KSTEP, id1, k != 0);
-            }
-          }
-          ptx::mma_commit(&s_full[g]);
-          ptx::mbar_wait(&p_ready[g], (uq >> 1) & 1);
-          ptx::mbar_wait(&v_full[slot], ph);
-          ptx::tc_fence_after();
-          {
-            const uint32_t idesc = ptx::idesc_bf16_f32(A2_BQ, DP) | (1u << 16);  // B (= V) is MN-major
-            const int ksteps = nk16 >> 4;
-            const uint64_t dv0 = desc_nosw(ptx::smem_u32(sV + slot * 2 * BLOCK), 128, CS);
-            constexpr uint64_t HALF = BLOCK >> 4;
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-              if (k < ksteps)
-                mma_f16_ts(tr + A2_OCOL, tr + (k < 8 ? 8 * k : 192 + 8 * (k - 8)), dv0 + (k >> 3) * HALF + (k & 7) * 16, idesc, k != 0);
-            }
-          }
-          ptx::mma_commit(&o_full[g]);
-          // K and V of the item are free once both groups' P V have retired (an item with one live unit arrives for both)
-          ptx::mma_commit(&kv_empty[slot]);
-          if (nlive == 1) ptx::mma_commit(&kv_empty[slot]);
+      // cursor over the live units in issue order; the NEXT unit of this group (incl. its kv_len load) is looked up while the softmax of
+      // the current one runs, and everything that does not depend on the awaited barrier is computed before the wait: this thread gets
+      // an issue slot only every ~20 clk next to the softmax warps of its scheduler, so each instruction after a barrier flip counts
+      struct It { int item, qt, nlive, uq, ic, nk16; bool valid; };
+      auto step = [&](It& it) {
+        if (it.qt + 1 < it.nlive) { ++it.qt; ++it.uq; return; }
+        for (;;) {
+          it.item += gridDim.x;
+          if (it.item >= n_items) { it.valid = false; return; }
+          const int kvl = min(kv_len[it.item / h], Tn);
+          const int nlive = min(upi, (kvl + A2_BQ - 1) / A2_BQ);
+          if (nlive == 0) continue;
+          it.nlive = nlive; it.nk16 = (kvl + 15) & ~15; it.qt = 0; ++it.uq; ++it.ic;
+          return;
         }
-        ++ic;
+      };
+      auto next_mine = [&](It& it) { do step(it); while (it.valid && (it.uq & 1) != g); };
+      It cur;
+      cur.item = (int)blockIdx.x - (int)gridDim.x; cur.qt = 0; cur.nlive = 0; cur.uq = -1; cur.ic = -1; cur.nk16 = 0; cur.valid = true;
+      next_mine(cur);
+      constexpr uint64_t KSTEP = (2 * CS) >> 4, HALF = BLOCK >> 4;   // descriptor start-address field is in 16-byte units
+      const uint32_t idpv = ptx::idesc_bf16_f32(A2_BQ, DP) | (1u << 16);  // B (= V) is MN-major
+      while (cur.valid) {
+        const int uq = cur.uq, slot = cur.ic & 1, qb = uq % A2_NQ;
+        const uint32_t ph = (cur.ic >> 1) & 1;
+        const int n0 = min(cur.nk16, 128), n1 = cur.nk16 - n0, ksteps = cur.nk16 >> 4, nlive = cur.nlive;
+        const uint64_t da0 = desc_nosw(ptx::smem_u32(sQ + qb * BLOCK), CS, 128);
+        const uint64_t db0 = desc_nosw(ptx::smem_u32(sK + slot * 2 * BLOCK), CS, 128);
+        const uint64_t dv0 = desc_nosw(ptx::smem_u32(sV + slot * 2 * BLOCK), 128, CS);
+        const uint32_t id0 = ptx::idesc_bf16_f32(A2_BQ, n0), id1 = ptx::idesc_bf16_f32(A2_BQ, n1 > 0 ? n1 : 16);
+        ptx::mbar_wait(&q_full[qb], (uq / A2_NQ) & 1);      // operands first (they land early), the TMEM region last
+        ptx::mbar_wait(&k_full[slot], ph);
+        ptx::mbar_wait(&t_empty[g], ((uq >> 1) & 1) ^ 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < DP / 16; ++k) ptx::mma_f16_ss(tr, da0 + k * KSTEP, db0 + k * KSTEP, id0, k != 0);
+        if (n1 > 0) {
+#pragma unroll
+          for (int k = 0; k < DP / 16; ++k) ptx::mma_f16_ss(tr + 128, da0 + k * KSTEP, db0 + HALF + k * KSTEP, id1, k != 0);
+        }
+        ptx::mma_commit(&s_full[g]);
+        It nxt = cur;
+        next_mine(nxt);                                       // hidden under the softmax of this unit
+        ptx::mbar_wait(&v_full[slot], ph);
+        ptx::mbar_wait(&p_ready[g], (uq >> 1) & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          if (k < ksteps)
+            mma_f16_ts(tr + A2_OCOL, tr + (k < 8 ? 8 * k : 192 + 8 * (k - 8)), dv0 + (k >> 3) * HALF + (k & 7) * 16, idpv, k != 0);
+        }
+        ptx::mma_commit(&o_full[g]);
+        // K and V of the item are free once both groups' P V have retired (an item with one live unit arrives for both)
+        ptx::mma_commit(&kv_empty[slot]);
+        if (nlive == 1) ptx::mma_commit(&kv_empty[slot]);
+        cur = nxt;
       }
     }
     __syncwarp();
