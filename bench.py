@@ -262,7 +262,19 @@ def run_cuda_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on STDOUT when the communicator is created (NCCL_DEBUG >= VERSION on the GPU boxes; WARN still
+        # prints it).  stdout carries exactly one JSON line, so file descriptor 1 points at stderr while the communicator comes up.
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     peaks = load_peaks()
     D, Hd, L, heads = MODELS[args.model]
     B = args.batch
