@@ -228,8 +228,65 @@ def main():
         if valid <= 256:
             hp[key + ".unpadded"] = mod._unpad_latent(padded, valid, h, w, 2).numpy()
     np.savez_compressed(os.path.join(OUT, "pad_helpers.npz"), **hp)
+    gen_masked(FiT, create_diffusion)
     print("goldens written to", OUT)
 
 
+from oracle.synth import MASKED_CFG, MASKED_SHAPES, masked_inputs  # noqa: E402
+
+
+def gen_masked(FiT, create_diffusion):
+    """masked_FiT: the reference's OWN ImageNetLatentIterator._patchify / subsample / collate (masked_FiT/preprocess/iterators.py:128-169,
+    called unbound: the class constructor needs dataset files) followed by its training-step arithmetic (masked_FiT/train.py:40-60) on
+    the reference model.  Pins row f4 (token sub-sampling in permuted order with the matching RoPE rows) and the masked leg of config 5."""
+    import importlib.util
+    import random
+    if "torchvision.transforms" not in sys.modules:
+        _stub("torchvision.transforms")
+    spec = importlib.util.spec_from_file_location("masked_iterators", "/root/reference/masked_FiT/preprocess/iterators.py")
+    mi = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mi)
+    it = mi.ImageNetLatentIterator.__new__(mi.ImageNetLatentIterator)
+    it.patch_size, it.C, it.embed_dim, it.embed_method = 2, 4, 72, "rotate"
+    lats, labels = masked_inputs()
+    batch = []
+    for lat, lab in zip(lats, labels):
+        tok, pos = it._patchify(lat)                                   # iterators.py:128-140
+        batch.append((torch.tensor(tok), [lab], torch.tensor(pos), torch.ones(tok.shape[0], dtype=torch.bool)))
+    out = {}
+    seed_py = next(s for s in range(100) if random.Random(s).choice([32, 64, 96, 128, 192, 256]) == 128)
+    random.seed(seed_py)                                               # collate draws number_of_tokens with random.choice (:158)
+    torch.manual_seed(11)                                              # subsample draws torch.randperm from the global generator (:144)
+    latent, label, pos, mask = it.collate(batch)
+    assert latent.shape[1] == 128
+    out["collate.latent"], out["collate.pos"], out["collate.mask"] = latent.numpy(), pos.numpy(), mask.numpy()
+    out["collate.label"] = label.numpy()
+    out["number_of_tokens"] = np.array(128)
+    # training step (masked_FiT/train.py:40-60); DDIMScheduler.add_noise restated by the reference's own q_sample (same linear schedule)
+    from oracle import fit_oracle as fo
+    sd = fo.random_state_dict(MASKED_CFG, seed=7)
+    ref = FiT(**MASKED_CFG)
+    ref.load_state_dict(sd)
+    ref.eval()
+    g = torch.Generator().manual_seed(17)
+    t = torch.randint(0, 1000, (latent.shape[0],), generator=g)
+    noise = torch.randn(latent.shape, generator=g)
+    x_t = create_diffusion("").q_sample(latent, t, noise=noise)
+    y = label.to(torch.int64).reshape(-1)
+    model_output = ref(x_t, t=t, y=y, pos=pos, mask=mask)
+    loss = torch.nn.functional.mse_loss(model_output[mask], noise[mask])
+    loss.backward()
+    out["x_t"], out["out_train"], out["loss"] = x_t.numpy(), model_output.detach().numpy(), np.array(float(loss))
+    for k, prm in ref.named_parameters():
+        out["gnorm." + k] = np.array(float(prm.grad.double().norm()))
+        out["g." + k] = prm.grad.numpy().copy()
+    np.savez_compressed(os.path.join(OUT, "masked_fit_tiny.npz"), **out)
+    print("masked_fit_tiny loss", float(loss), "valid tokens", int(mask.sum()))
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "masked":   # only the masked_FiT fixture (the others are unchanged)
+        FiT_, _, create_diffusion_, _ = import_reference()
+        gen_masked(FiT_, create_diffusion_)
+    else:
+        main()

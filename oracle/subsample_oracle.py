@@ -1,6 +1,9 @@
 """TEST INFRASTRUCTURE ONLY: CPU restatement of masked_FiT's ImageNetLatentIterator.subsample + collate stacking
 (masked_FiT/preprocess/iterators.py:142-169) with torch on CPU.  The reference class needs its dataset files to be constructed, so the
-two methods are restated (12 lines); the RNG calls (torch.randperm per over-long sample, in batch order) are the reference's."""
+two methods are restated (12 lines); the RNG calls (torch.randperm per over-long sample, in batch order) are the reference's.
+PINNED: oracle/make_goldens.py::gen_masked calls the reference's own _patchify / subsample / collate unbound (object made with __new__)
+and tests/test_oracle_golden.py::test_masked_fit_collate_and_training_step_match_reference checks this restatement against that output
+bit for bit (tests/golden/masked_fit_tiny.npz)."""
 import torch
 
 

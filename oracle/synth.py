@@ -72,3 +72,40 @@ def masked_batch(cfg, shapes, n_tokens, seed, rope_dim, T_ntk=256):
     y = torch.randint(0, cfg["num_classes"], (N,), generator=g)
     target = torch.randn(N, n_tokens, p * p * cfg["in_channels"], generator=g)
     return x, t, y, pos, mask, target
+
+
+# ---- masked_FiT fixture (tests/golden/masked_fit_tiny.npz, written by oracle/make_goldens.py::gen_masked from the reference's own
+# ImageNetLatentIterator._patchify / subsample / collate and training step)
+MASKED_SHAPES = [(32, 32), (32, 32), (20, 40), (8, 16)]   # 256, 256, 200 tokens (sub-sampled to 128) and 32 tokens (padded)
+MASKED_CFG = dict(patch_size=2, in_channels=4, hidden_size=144, depth=2, num_heads=2, mlp_ratio=4.0,
+                  class_dropout_prob=0.1, num_classes=10, learn_sigma=False)   # head_dim 72, like FiT-XL/2
+
+
+def masked_inputs(seed=31):
+    """Seeded dataset items in the form masked_FiT's __getitem__ hands to collate (iterators.py:171-186): raw latents + labels."""
+    g = torch.Generator().manual_seed(seed)
+    lats = [torch.randn(4, h, w, generator=g).numpy() for (h, w) in MASKED_SHAPES]
+    labels = [int(v) for v in torch.randint(0, 10, (len(MASKED_SHAPES),), generator=g)]
+    return lats, labels
+
+
+def masked_items(seed=31):
+    """The same items after the iterator's _patchify (iterators.py:128-140): token rows, RoPE rows (table built WITHOUT max_length,
+    i.e. fp32-precision frequencies, as the iterator does), all-ones masks.  Returns (latents, poss, masks, labels) as host tensors."""
+    lats, labels = masked_inputs(seed)
+    toks, poss, masks = [], [], []
+    for lat in lats:
+        tok = fo.patchify(torch.tensor(lat)[None], 2)[0]
+        h, w = lat.shape[1] // 2, lat.shape[2] // 2
+        toks.append(tok.contiguous())
+        poss.append(torch.tensor(precompute_freqs_cis_2d(72, h, w).astype("float32")))
+        masks.append(torch.ones(tok.shape[0], dtype=torch.bool))
+    return toks, poss, masks, labels
+
+
+def masked_step_noise(shape, seed=17):
+    """t and noise of the masked training-step fixture (drawn in the order gen_masked draws them)."""
+    g = torch.Generator().manual_seed(seed)
+    t = torch.randint(0, 1000, (shape[0],), generator=g)
+    noise = torch.randn(shape, generator=g)
+    return t, noise

@@ -34,3 +34,15 @@ def build_model(cfg, sd, precision, device="cuda", train_mode=False):
 def dev(*ts, device="cuda"):
     out = [t.to(device) if isinstance(t, torch.Tensor) else t for t in ts]
     return out if len(out) > 1 else out[0]
+
+
+def record(key, value):
+    """Append a measured parity figure (worst-case error of a test) to gpurun_out/parity_measured.txt so the GPU run leaves the actual
+    numbers behind, not only pass/fail against the bound (copied to profiles/ per round)."""
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "parity_measured.txt"), "a") as fh:
+            fh.write(f"{key}\t{value}\n")
+    except OSError:
+        pass

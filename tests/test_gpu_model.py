@@ -232,11 +232,12 @@ def test_headline_size_properties():
     assert float((full.cpu() - z).abs().mean()) > 1e-3
 
 
-@pytest.mark.parametrize("model_name,depth,hw", [("FiT-B/2", 2, (40, 40)), ("FiT-XL/2", 1, (40, 48)), ("FiT-B/2", 1, (64, 80))])
+@pytest.mark.parametrize("model_name,depth,hw", [("FiT-B/2", 2, (40, 40)), ("FiT-XL/2", 1, (40, 48)), ("FiT-B/2", 1, (64, 80)),
+                                                 ("FiT-XL/2", 1, (128, 128))])
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16", 2e-2)])
 def test_resolution_extrapolation_forward_matches_oracle(model_name, depth, hw, precision, tol):
     """BASELINE config 5, extrapolation leg: more than max_length = 256 tokens in one image (320x320 -> 400 tokens, 320x384 -> 480,
-    512x640 -> 1280) with the VisionNTK-scaled RoPE table (FiT/train.py:136-156).  The bf16 path runs the KV-blocked tcgen05
+    512x640 -> 1280, 1024x1024 -> 4096 with NTK scale 3.9375) with the VisionNTK-scaled RoPE table (FiT/train.py:136-161).  The bf16 path runs the KV-blocked tcgen05
     attention (attn_tc3.cu); compared with the CPU oracle on the same weights and inputs (the oracle itself is pinned to the reference
     goldens at <= 256 tokens; the sequence length only changes the table and the attention span)."""
     cfg = fo.model_config(model_name, depth=depth)
@@ -251,5 +252,7 @@ def test_resolution_extrapolation_forward_matches_oracle(model_name, depth, hw, 
     with torch.no_grad():
         got = model(zz.cuda(), tt.cuda(), yy.cuda(), pos.cuda(), mask.cuda(), train=False)
         got_cfg = model.forward_with_cfg(zz.cuda(), tt.cuda(), yy.cuda(), pos.cuda(), mask.cuda(), 1.5)
+    from helpers import record
+    record(f"extrapolation forward {model_name} x{depth} {h}x{w} [{precision}] rel-L2", f"{rel_l2(got, want):.3e}")
     assert rel_l2(got, want) < tol
     assert rel_l2(got_cfg, want_cfg) < tol

@@ -190,3 +190,33 @@ def test_padded_tokens_do_not_influence_valid_tokens():
         x2 = x.clone(); x2[~mask] = torch.randn_like(x2[~mask]) * 100
         b = fo.forward(sd, cfg, x2, t, y, pos, mask)
     assert torch.equal(a[mask], b[mask])
+
+
+def test_masked_fit_collate_and_training_step_match_reference():
+    """masked_FiT (row f4 + the masked leg of config 5): the restated subsample / collate reproduces, bit for bit, what the reference's
+    own ImageNetLatentIterator._patchify + collate produced from the same items and RNG seeds (tokens in permuted order with their RoPE
+    rows, padding for the short sample), and the oracle's training-step arithmetic on that batch matches the reference's loss and every
+    parameter gradient (masked_FiT/train.py:40-60)."""
+    from oracle.subsample_oracle import collate
+    z = np.load(os.path.join(G, "masked_fit_tiny.npz"))
+    toks, poss, masks, labels = synth.masked_items()
+    T2 = int(z["number_of_tokens"])
+    lat, pos, msk = collate(toks, poss, masks, T2, generator=torch.Generator().manual_seed(11))
+    assert torch.equal(lat, torch.from_numpy(z["collate.latent"]))
+    assert torch.equal(pos, torch.from_numpy(z["collate.pos"]))
+    assert torch.equal(msk, torch.from_numpy(z["collate.mask"]))
+    assert [int(v) for v in z["collate.label"].reshape(-1)] == labels
+    assert int(msk.sum()) == 3 * 128 + 32 and not bool(msk[3, 32:].any())
+    # the kept tokens are NOT a prefix of the image: the permuted RoPE rows are what tells the network where they came from
+    assert not torch.equal(pos[0], poss[0][:T2])
+    t, noise = synth.masked_step_noise(lat.shape)
+    tb, _ = do.create("")
+    x_t = do.q_sample(tb, lat, t, noise)
+    assert rel_l2(x_t, z["x_t"]) < 1e-6
+    cfg = synth.MASKED_CFG
+    sd = fo.random_state_dict(cfg, seed=7)
+    loss, out, grads = fo.loss_and_grads(sd, cfg, x_t, t, torch.tensor(labels), pos, msk, noise)
+    assert rel_l2(out[msk], torch.from_numpy(z["out_train"])[msk]) < 2e-6
+    assert abs(float(loss) - float(z["loss"])) < 1e-5 * abs(float(z["loss"]))
+    for k, g in grads.items():
+        assert rel_l2(g, z["g." + k]) < 2e-5, k
