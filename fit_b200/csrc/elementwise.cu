@@ -469,8 +469,10 @@ __device__ __forceinline__ void philox4x32_10(uint32_t (&c)[4], uint32_t k0, uin
 }
 
 __global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ out, int rows, long per_row, uint64_t seed,
-                                                            const int64_t* __restrict__ step_ptr, long row_offset) {
+                                                            const int64_t* __restrict__ step_ptr, long row_offset,
+                                                            const int64_t* __restrict__ row_offset_ptr) {
   const long nvec = (long)rows * per_row / 4;
+  if (row_offset_ptr) row_offset += (long)row_offset_ptr[0];  // device-resident part of the key: a replayed graph serves any batch position
   const uint64_t step = (uint64_t)(step_ptr ? step_ptr[0] : 0);
   const uint32_t k0 = (uint32_t)seed ^ (uint32_t)(step * 0x9E3779B97F4A7C15ull >> 32);
   const uint32_t k1 = (uint32_t)(seed >> 32) ^ (uint32_t)step;
@@ -672,11 +674,11 @@ int fitb200_q_sample(const float* x0, const float* noise, float* out, int rows, 
   return FITB200_OK;
 }
 
-int fitb200_philox_normal(float* out, int rows, int64_t per_row, uint64_t seed, const int64_t* step, int64_t row_offset,
+int fitb200_philox_normal(float* out, int rows, int64_t per_row, uint64_t seed, const int64_t* step, int64_t row_offset, const int64_t* row_offset_dev,
                           fitb200_stream_t stream) {
   FITB200_CHECK_ARG(out && rows > 0 && per_row > 0 && per_row % 4 == 0 && row_offset >= 0, "philox_normal: bad arguments");
   long nvec = (long)rows * per_row / 4;
-  philox_normal_kernel<<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(out, rows, per_row, seed, step, row_offset);
+  philox_normal_kernel<<<step_grid(nvec), 256, 0, (cudaStream_t)stream>>>(out, rows, per_row, seed, step, row_offset, row_offset_dev);
   FITB200_CHECK_LAUNCH("philox_normal");
   return FITB200_OK;
 }

@@ -171,7 +171,7 @@ class FiTEngine:
         R, T, D = ws.R, ws.T, m.hidden_size
         e = W.blocks[i]
         sh1, sc1, g1, sh2, sc2, g2 = ws.mod_views[i]
-        nm = W.n_mod
+        nm = ws.mod.stride(0)
         ops.ln_modulate(ws.xs, sh1, sc1, nm, T, ws.h)
         if self.precision == "bf16":
             # apply_rotary_emb (fit.py:160-174) rides in the qkv GEMM epilogue (fp32 accumulators, q and k columns), so the
@@ -188,6 +188,113 @@ class FiTEngine:
         else:
             ops.gemm(ws.h, e["fc1_g_w"], e["fc1_g_b"], ws.g, EPI_SWIGLU, B2=e["fc1_x_w"], bias2=e["fc1_x_b"])
         ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=nm, rows_per_sample=T, resid=ws.xs)
+
+    # ------------------------------------------------------------------ sub-module entry points (fit.py:229-250,277-285,326-337; dit.py:138-142)
+    class _Scratch:
+        """Buffers of one stand-alone sub-module call (same fields FiTEngine.block reads from a _Workspace)."""
+        pass
+
+    def _scratch(self, x: Tensor, mask: Optional[Tensor], Hp: int):
+        R, T, D = x.shape
+        M, act, dev = R * T, self.act_dtype, x.device
+        ws = FiTEngine._Scratch()
+        ws.R, ws.T = R, T
+        ws.xs = ops.cast(x.reshape(M, D).contiguous(), torch.empty(M, D, dtype=act, device=dev)) if x.dtype != act else x.reshape(M, D).clone()
+        ws.h = torch.empty(M, D, dtype=act, device=dev)
+        ws.qkv = torch.empty(M, 3 * D, dtype=act, device=dev)
+        ws.att = torch.empty(M, D, dtype=act, device=dev)
+        ws.g = torch.zeros(M, Hp, dtype=act, device=dev)
+        if mask is None:
+            mask = torch.ones(R, T, dtype=torch.bool, device=dev)
+        ws.mask = mask
+        ws.kv_len, ws.n_valid = ops.mask_to_kvlen(mask)
+        return ws
+
+    def _check_sub(self, x: Tensor):
+        if x.dim() != 3 or x.shape[2] != self.model.hidden_size:
+            raise ValueError(f"expected x of shape (batch, tokens, {self.model.hidden_size}), got {tuple(x.shape)}")
+        if x.dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError("fit_b200: x must be fp32 or bf16")
+        if not x.is_cuda:
+            raise RuntimeError("fit_b200 kernels need CUDA tensors (there is no CPU fallback)")
+
+    def _modulation(self, c: Tensor, w: Tensor, b: Tensor) -> Tensor:
+        """adaLN_modulation(c) = Linear(SiLU(c)) (fit.py:323-324,329; dit.py:134-139) for ONE block / the final layer -> fp32 [R, n]."""
+        c32 = c.float().contiguous()
+        sc = ops.silu_fwd(c32, torch.empty_like(c32))
+        if self.act_dtype != torch.float32:
+            sc = ops.cast(sc, torch.empty(c32.shape, dtype=self.act_dtype, device=c.device))
+        return ops.gemm(sc, w, b, torch.empty(c.shape[0], w.shape[0], dtype=torch.float32, device=c.device), EPI_BIAS)
+
+    def _pos(self, freqs_cis: Optional[Tensor], R: int, T: int) -> Tensor:
+        d = self.model.hidden_size // self.model.num_heads
+        if freqs_cis is None:
+            raise ValueError("fit_b200: freqs_cis (the RoPE table) is required: every FiT block is built with pos='rotate'")
+        pos = freqs_cis if freqs_cis.dim() == 3 else freqs_cis[None]
+        if pos.shape[0] not in (1, R) or pos.shape[1] != T or pos.shape[2] != d or pos.dtype != torch.float32:
+            raise ValueError(f"freqs_cis {tuple(pos.shape)} {pos.dtype} does not match (1|{R}, {T}, {d}) fp32")
+        return pos.contiguous()
+
+    def _out(self, buf: Tensor, like: Tensor, shape) -> Tensor:
+        if buf.dtype != like.dtype:
+            buf = ops.cast(buf, torch.empty(buf.shape, dtype=like.dtype, device=buf.device))
+        return buf.view(*shape)
+
+    def run_block(self, i: int, x: Tensor, c: Tensor, mask: Optional[Tensor], freqs_cis: Optional[Tensor]) -> Tensor:
+        """FiTBlock.forward(x, c, mask, freqs_cis) (fit.py:326-337) on caller tensors: same kernels as the whole-network path."""
+        self._check_sub(x)
+        W = self.weights()
+        D = self.model.hidden_size
+        R, T, _ = x.shape
+        ws = self._scratch(x, mask, W.Hp)
+        ws.mod = self._modulation(c, W.ada_w[6 * i * D:6 * (i + 1) * D], W.ada_b[6 * i * D:6 * (i + 1) * D])
+        ws.mod_views = {i: [ws.mod[:, k * D:(k + 1) * D] for k in range(6)]}
+        self.block(i, ws, W, self._pos(freqs_cis, R, T), ws.mask)
+        return self._out(ws.xs, x, x.shape)
+
+    def run_attention(self, i: int, x: Tensor, mask: Optional[Tensor], freqs_cis: Optional[Tensor]) -> Tensor:
+        """SelfAttention.forward(x, mask, freqs_cis) (fit.py:229-250): qkv GEMM (+RoPE), attention, proj GEMM (+bias)."""
+        self._check_sub(x)
+        W, m = self.weights(), self.model
+        e = W.blocks[i]
+        R, T, D = x.shape
+        ws = self._scratch(x, mask, 16)
+        pos = self._pos(freqs_cis, R, T)
+        h, d = m.num_heads, D // m.num_heads
+        if self.precision == "bf16":
+            ops.gemm(ws.xs, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS_ROPE, rope=pos, rope_cols=2 * D)
+            ops.attention(ws.qkv, None, ws.kv_len, ws.mask, R, T, h, d, ws.att, prerotated=True)
+        else:
+            ops.gemm(ws.xs, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS)
+            ops.attention(ws.qkv, pos, ws.kv_len, ws.mask, R, T, h, d, ws.att)
+        ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.h, EPI_BIAS)
+        return self._out(ws.h, x, x.shape)
+
+    def run_ffn(self, i: int, x: Tensor) -> Tensor:
+        """SwiGLU.forward(x) (fit.py:277-285): fc2(silu(fc1_g(x)) * fc1_x(x))."""
+        self._check_sub(x)
+        W = self.weights()
+        e = W.blocks[i]
+        ws = self._scratch(x, None, W.Hp)
+        if self.precision == "bf16":
+            ops.gemm(ws.xs, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU)
+        else:
+            ops.gemm(ws.xs, e["fc1_g_w"], e["fc1_g_b"], ws.g, EPI_SWIGLU, B2=e["fc1_x_w"], bias2=e["fc1_x_b"])
+        ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.h, EPI_BIAS)
+        return self._out(ws.h, x, x.shape)
+
+    def run_final_layer(self, x: Tensor, c: Tensor) -> Tensor:
+        """FinalLayer.forward(x, c) (dit.py:138-142): tokens [R, T, D] -> [R, T, p*p*C_out]."""
+        self._check_sub(x)
+        W, m = self.weights(), self.model
+        R, T, D = x.shape
+        L = len(m.blocks)
+        ws = self._scratch(x, None, 16)
+        mod = self._modulation(c, W.ada_w[6 * L * D:], W.ada_b[6 * L * D:])
+        P = m.patch_size * m.patch_size * m.out_channels
+        out = torch.empty(R, T, P, dtype=torch.float32, device=x.device)
+        ops.final_layer(ws.xs, mod[:, :D], mod[:, D:], mod.stride(0), W.fin_w, W.fin_b, out, R, T, m.patch_size, m.out_channels)
+        return out if x.dtype == torch.float32 else out.to(x.dtype)
 
     # ------------------------------------------------------------------ forward
     def forward(self, x: Tensor, t: Tensor, y: Tensor, pos: Tensor, mask: Tensor, train: bool = True,

@@ -66,6 +66,8 @@ class TimestepEmbedder(nn.Module):
 
     def __init__(self, hidden_size: int, frequency_embedding_size: int = 256):
         super().__init__()
+        if frequency_embedding_size != 256:
+            raise NotImplementedError("fit_b200: the timestep kernels are built for frequency_embedding_size = 256 (every FiT model, fit.py:55)")
         self.mlp = nn.Sequential(Linear(frequency_embedding_size, hidden_size), SiLU(), Linear(hidden_size, hidden_size))
         self.frequency_embedding_size = frequency_embedding_size
 
@@ -100,6 +102,16 @@ class LabelEmbedder(nn.Module):
         return labels
 
 
+def _owner(mod: nn.Module):
+    """(engine, block index) of the FiT model a sub-module belongs to (set by FiT.__init__: a plain attribute, not a registered child,
+    so state_dict / .to() / named_modules never see it; deepcopy and pickle follow it like the engine's own back-reference)."""
+    ref = getattr(mod, "_fit_owner", None)
+    fit = ref[0] if ref is not None else None
+    if fit is None:
+        raise RuntimeError("fit_b200: this sub-module runs on the kernels of the FiT model that owns it; build it through FiT(...)")
+    return fit.engine, ref[1]
+
+
 class SelfAttention(nn.Module):
     """fit.py:191-250 (parameters ``qkv``, ``proj``)."""
 
@@ -117,6 +129,11 @@ class SelfAttention(nn.Module):
         self.proj = Linear(dim, dim)
         self.apply_rotate_embed = apply_rotate_embed
 
+    def forward(self, x: Tensor, mask: Optional[Tensor] = None, freqs_cis: Optional[Tensor] = None) -> Tensor:
+        """fit.py:229-250 on caller tensors (inference only: the differentiable path is the whole-network autograd node)."""
+        eng, i = _owner(self)
+        return eng.run_attention(i, x, mask, freqs_cis)
+
 
 class SwiGLU(nn.Module):
     """fit.py:253-285 (parameters ``fc1_g``, ``fc1_x``, ``fc2``)."""
@@ -130,6 +147,11 @@ class SwiGLU(nn.Module):
         self.fc1_g = Linear(in_features, hidden_features, bias=bias)
         self.fc1_x = Linear(in_features, hidden_features, bias=bias)
         self.fc2 = Linear(hidden_features, out_features, bias=bias)
+
+    def forward(self, x: Tensor) -> Tensor:
+        """fit.py:277-285 on caller tensors (inference only)."""
+        eng, i = _owner(self)
+        return eng.run_ffn(i, x)
 
 
 class FiTBlock(nn.Module):
@@ -150,6 +172,12 @@ class FiTBlock(nn.Module):
             raise ValueError(f"Unsupported ffn `{ffn}`")
         self.adaLN_modulation = nn.Sequential(SiLU(), Linear(hidden_size, 6 * hidden_size))
 
+    def forward(self, x: Tensor, c: Tensor, mask: Optional[Tensor] = None, freqs_cis: Optional[Tensor] = None) -> Tensor:
+        """fit.py:326-337 on caller tensors: x [B, N, D], c [B, D], mask [B, N] bool, freqs_cis [1|B, N, head_dim] fp32 -> [B, N, D]
+        (inference only: hooks / per-block probing; training differentiates through FiT.forward's single autograd node)."""
+        eng, i = _owner(self)
+        return eng.run_block(i, x, c, mask, freqs_cis)
+
 
 class FinalLayer(nn.Module):
     """models/dit.py:125-142 (parameters ``linear``, ``adaLN_modulation.1``)."""
@@ -158,6 +186,11 @@ class FinalLayer(nn.Module):
         super().__init__()
         self.linear = Linear(hidden_size, patch_size * patch_size * out_channels)
         self.adaLN_modulation = nn.Sequential(SiLU(), Linear(hidden_size, 2 * hidden_size))
+
+    def forward(self, x: Tensor, c: Tensor) -> Tensor:
+        """dit.py:138-142 on caller tensors (inference only)."""
+        eng, _ = _owner(self)
+        return eng.run_final_layer(x, c)
 
 
 class FiT(nn.Module):
@@ -189,6 +222,10 @@ class FiT(nn.Module):
         self.final_layer = FinalLayer(hidden_size, patch_size, self.out_channels)
         self.initialize_weights()
         self._engine = FiTEngine(self, precision or os.environ.get("FITB200_PRECISION", "bf16"))
+        for i, blk in enumerate(self.blocks):
+            for sub in (blk, blk.attn, blk.ffn):
+                sub._fit_owner = (self, i)
+        self.final_layer._fit_owner = (self, depth)
 
     # ------------------------------------------------------------------ init (fit.py:404-430)
     def initialize_weights(self):
@@ -240,7 +277,8 @@ class FiT(nn.Module):
     def forward(self, x: Tensor, t: Tensor, y: Tensor, pos: Tensor, mask: Tensor, train=True) -> Tensor:
         """fit.py:474-518.  train=True: tokens (N,T,p*p*C) in and out; train=False: latents (N,C,H,W) in and out
         (patchify / unpatchify are fused into the embedder / final-layer kernels)."""
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and self.training:
+        # autograd whenever gradients are wanted -- eval-mode fine-tuning / guidance included (label dropout keys off self.training alone)
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
             from ..train import fit_forward_autograd
             return fit_forward_autograd(self, x, t, y, pos, mask, train)
         y = self.y_embedder.labels_for(y, self.training)

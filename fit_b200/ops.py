@@ -197,13 +197,18 @@ def q_sample(x0: Tensor, noise: Tensor, t: Tensor, sqrt_ac: Tensor, sqrt_1m_ac: 
     return out
 
 
-def philox_normal(out: Tensor, seed: int, step: Optional[Tensor], row_offset: int = 0):
-    """out[rows, ...] <- N(0,1) keyed by (seed, step[0], global row index)."""
+def philox_normal(out: Tensor, seed: int, step: Optional[Tensor], row_offset=0):
+    """out[rows, ...] <- N(0,1) keyed by (seed, step[0], global row index).  row_offset: int, or a 1-element int64 device tensor
+    (read at run time: a captured graph then serves any batch position)."""
     L.require_cuda(out)
     assert out.dtype == torch.float32 and out.is_contiguous()
     rows = out.shape[0]
-    L.check(L.lib().fitb200_philox_normal(L.ptr(out), rows, out.numel() // rows, seed & (2 ** 64 - 1), L.ptr(step), row_offset,
-                                          L.stream_ptr()), "philox_normal")
+    off_dev = None
+    if isinstance(row_offset, torch.Tensor):
+        assert row_offset.dtype == torch.int64 and row_offset.is_cuda
+        off_dev, row_offset = row_offset, 0
+    L.check(L.lib().fitb200_philox_normal(L.ptr(out), rows, out.numel() // rows, seed & (2 ** 64 - 1), L.ptr(step), int(row_offset),
+                                          L.ptr(off_dev), L.stream_ptr()), "philox_normal")
     return out
 
 

@@ -129,9 +129,33 @@ class FusedAdamWEMA:
                 "ema": self.ema_params, "current_step": self.step_count, "decay": self.ema_decay, "every_n_steps": self.every_n_steps}
 
     def load_state_dict(self, sd):
-        for i, st in sd["state"].items():
+        """Accepts this class's own ``state_dict()``, the reference EMA optimizer's layout ``{"opt": AdamW state, "ema", "current_step",
+        "decay", "every_n_steps"}`` (FiT/ema.py:322-347 -- what ``checkpoint.to_lightning_checkpoint`` writes into ``optimizer_states[0]``)
+        and a bare ``torch.optim.AdamW`` state dict.  Restores the moments, the step count (``current_step``, else the per-parameter
+        ``step`` AdamW keeps) and the EMA copy, so a resumed run continues with the right bias correction."""
+        opt = sd["opt"] if "opt" in sd else sd
+        steps = []
+        for i, st in opt["state"].items():
             self.exp_avg[int(i)].copy_(st["exp_avg"]); self.exp_avg_sq[int(i)].copy_(st["exp_avg_sq"])
-        self.step_count = int(sd.get("current_step", 0))
+            if "step" in st:
+                steps.append(int(float(st["step"])))
+        if sd.get("current_step") is not None:
+            self.step_count = int(sd["current_step"])
+        elif steps:
+            self.step_count = max(steps)
+        else:
+            self.step_count = 0
+        groups = opt.get("param_groups") or []
+        if groups:
+            g0 = groups[0]
+            self.lr, self.betas = g0.get("lr", self.lr), tuple(g0.get("betas", self.betas))
+            self.eps, self.weight_decay = g0.get("eps", self.eps), g0.get("weight_decay", self.weight_decay)
+        if sd.get("decay") is not None:
+            self.ema_decay = sd["decay"]
+        if sd.get("every_n_steps") is not None:
+            self.every_n_steps = sd["every_n_steps"]
         if sd.get("ema") is not None and self.ema_params:
+            if len(sd["ema"]) != len(self.ema_params):
+                raise ValueError(f"EMA state holds {len(sd['ema'])} tensors, the optimizer has {len(self.ema_params)} parameters")
             for e, src in zip(self.ema_params, sd["ema"]):
                 e.copy_(src)

@@ -52,7 +52,14 @@ class CFGSampler:
         self.step_scalar = torch.empty(1, dtype=torch.int64, device=dev)
         self.use_graph = use_graph
         self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._captured = None          # (engine, packed weights, workspace) the graph holds raw pointers into: kept alive, compared per run
+        self.captures = 0              # number of graph captures so far (tests assert one per bucket)
         self.launches_per_step = 0
+        # the embedding table has a null-class row only when the model was built with class_dropout_prob > 0 (fit.py:94-95): without it the
+        # reference's unconditional half raises an index error -- do the same instead of sampling a wrong class
+        if model.y_embedder.embedding_table.weight.shape[0] <= model.y_embedder.num_classes:
+            raise IndexError("CFG sampling needs the null-class embedding row (class_dropout_prob > 0); this model has none")
+        self.row_offset_dev = torch.tensor([int(row_offset)], dtype=torch.int64, device=dev)   # read by the noise kernel at run time
 
     # ------------------------------------------------------------------ one step (all C-ABI launches)
     def _step(self):
@@ -60,7 +67,7 @@ class CFGSampler:
         tb = d._tables(self.device)
         ops.gather_i64(d._map_tensor(self.device), self.t_idx, self.t_model)
         m.engine.forward(self.x, self.t_model, self.y, self.pos, self.mask, train=False, rows=2 * self.B, out=self.raw)
-        ops.philox_normal(self.noise, self.seed, self.t_idx, self.row_offset)
+        ops.philox_normal(self.noise, self.seed, self.t_idx, self.row_offset_dev)
         ops.cfg_step(self.x, self.raw, self.noise, self.t_idx[: self.B], tb["coef"], cfg_pairs=self.B, cfg_scale=self.cfg_scale,
                      ddim=(self.mode == "ddim"), eta=self.eta, flags=d._flags(self.clip), sample=self.x)
         ops.add_i64(self.t_idx, -1)
@@ -75,6 +82,11 @@ class CFGSampler:
         out = torch.empty(rows, *self.x.shape[1:], dtype=torch.float32, device=self.device)
         self.step_scalar.fill_(i)
         return ops.philox_normal(out, self.seed, self.step_scalar, self.row_offset + row_offset)
+
+    def set_row_offset(self, row_offset: int):
+        """Global index of this sampler's first image (the noise key).  Device-resident: changing it does NOT re-capture the graph."""
+        self.row_offset = int(row_offset)
+        self.row_offset_dev.fill_(self.row_offset)
 
     # ------------------------------------------------------------------ driver
     def load(self, z: Tensor, y: Tensor, pos: Tensor, mask: Optional[Tensor] = None):
@@ -102,6 +114,11 @@ class CFGSampler:
                 for _ in range(n):
                     self._step()
                 return
+            eng = self.model.engine
+            if self._graph is not None and (eng is not self._captured[0] or eng.weights() is not self._captured[1]):
+                # parameters changed (load_state_dict, optimizer step, EMA swap: new packed weights) or set_precision() built a new
+                # engine: the captured pointers are stale
+                self._graph = None
             if self._graph is None:
                 # warm-up outside capture: workspace allocation, weight packing, cudaFuncSetAttribute
                 saved = (self.x.clone(), self.t_idx.clone())
@@ -112,6 +129,9 @@ class CFGSampler:
                 with torch.cuda.graph(g):
                     self._step()
                 self._graph = g
+                self.captures += 1
+                # strong references: an evicted workspace / repacked weight set must outlive the graph that points into it
+                self._captured = (eng, eng.weights(), eng.workspace(2 * self.B, self.T, self.device))
                 self.x.copy_(saved[0]); self.t_idx.copy_(saved[1])
             for _ in range(n):
                 self._graph.replay()
@@ -174,7 +194,7 @@ class SamplingDriver:
             s = CFGSampler(self.model, self.diffusion, batch=B, latent_hw=(h, w), cfg_scale=self.cfg_scale, seed=self.seed, mode=self.mode,
                            eta=self.eta)
             self._samplers[key] = s
-        s.row_offset = row_offset   # read at launch time by the noise kernel: part of the captured arguments, so re-capture
+        s.set_row_offset(row_offset)   # device-resident noise key: one captured graph per (batch, H, W) bucket serves every batch
         return s
 
     def sample(self, num_samples: int, image_hw: Tuple[int, int], batch_size: int = 100, num_classes: int = 1000,
@@ -192,9 +212,6 @@ class SamplingDriver:
             b0, b1 = shard_rows(cur, self.world, self.rank)
             if b1 > b0:
                 s = self._sampler(b1 - b0, H, W, row_offset=done + b0)
-                if s._graph is not None and getattr(s, "_captured_offset", None) != s.row_offset:
-                    s._graph = None                                  # the noise key (global image index) is a captured scalar
-                s._captured_offset = s.row_offset
                 outs.append(s.sample(z_all[b0:b1].pin_memory(), y_all[b0:b1].to(torch.int64).pin_memory(), pos))
                 labs.append(y_all[b0:b1])
             done += cur

@@ -92,7 +92,9 @@ class GradSync:
     flat fp32 bucket per block and all-reduced (NCCL over NVLink / NVSwitch on GPUs, gloo in the CPU tests) on a side stream
     while the backward of the earlier blocks keeps the compute stream busy.  ``finish`` joins the side stream, scales by
     1 / world_size and scatters the averaged values back into the gradient tensors autograd returns.
-    ``no_sync`` skips the exchange on non-final accumulation micro-steps (accumulate_grad_batches=2, FiT/train.py:288)."""
+    ``no_sync`` skips the exchange on non-final accumulation micro-steps (accumulate_grad_batches=2, FiT/train.py:288): autograd keeps
+    adding those micro-steps' local gradients into ``p.grad``; on the synced micro-step the accumulated ``p.grad`` is folded into the
+    bucket BEFORE the collective (and cleared), so every rank ends with mean_over_ranks(g_1 + ... + g_k) like torch DDP."""
 
     def __init__(self, process_group=None, bucket_bytes: int = 0):
         import torch.distributed as dist
@@ -103,6 +105,7 @@ class GradSync:
         self.enabled = True
         self._pending: List = []
         self._stream = None
+        self._params: Dict[str, torch.nn.Parameter] = {}
         # NCCL's CTAs need SMs of their own next to the persistent GEMM / attention grids: leave `reserve_sms` free while syncing.
         # (Set NCCL_MAX_CTAS <= reserve_sms before the process group is created to hold NCCL to that budget.)
         self.reserve_sms = int(os.environ.get("FITB200_DDP_RESERVE_SMS", "8")) if self.world > 1 and self.avg_in_collective else 0
@@ -113,6 +116,7 @@ class GradSync:
 
     def attach(self, model):
         object.__setattr__(model, "_grad_sync", self)
+        self._params = dict(model.named_parameters())
         return self
 
     class _NoSync:
@@ -128,6 +132,12 @@ class GradSync:
         it is all-reduced in place, with no packing copy before and no scatter copy after."""
         if not self.enabled or self.world == 1:
             return
+        # gradients accumulated under no_sync() by earlier micro-steps join the exchange: reduce (accumulated + new), not only the new part
+        for name, g in grads.items():
+            prm = self._params.get(name)
+            if prm is not None and prm.grad is not None:
+                g.add_(prm.grad)     # same accumulation autograd itself performs; g is a view into `flat` when the bucket is in place
+                prm.grad = None
         tensors = list(grads.values())
         in_place = flat is not None
         if not in_place:

@@ -191,10 +191,11 @@ int fitb200_q_sample(const float* x0, const float* noise, float* out, int rows, 
 /* Per-step Gaussian noise of p_sample (th.randn_like, gaussian_diffusion.py:422) as a counter-based generator:
  * Philox4x32-10 keyed by (seed, *step), counter = (row_offset + row) * per_row/4 + i, Box-Muller -> N(0,1).
  * Keyed by the GLOBAL image index so that a batch sharded over several GPUs draws, per image, exactly the
- * noise of the unsharded run; `step` is read from device memory (CUDA-graph replay).  Not the torch
+ * noise of the unsharded run; `step` and (optionally) `row_offset_dev[0]`, which is added to `row_offset`, are read from device
+ * memory, so ONE captured CUDA graph serves every step and every batch position (sample_lightning.py:32-70 loop).  Not the torch
  * generator's stream: parity tests pass the reference's noise explicitly instead. */
 int fitb200_philox_normal(float* out, int rows, int64_t per_row, uint64_t seed, const int64_t* step, int64_t row_offset,
-                          fitb200_stream_t stream);
+                          const int64_t* row_offset_dev, fitb200_stream_t stream);
 
 /* loop plumbing for CUDA-graph replay of the sampling loop (gaussian_diffusion.py:679, respace.py:125-126):
  * out[i] = map[clamp(idx[i])]; and idx[i] += delta. */

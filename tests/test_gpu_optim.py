@@ -78,3 +78,53 @@ def test_masked_subsample_matches_reference_collate(number_of_tokens):
     got = subsample_batch(lat, pos, msk, number_of_tokens, "cuda", generator=torch.Generator().manual_seed(11))
     for w, o in zip(want, got):
         assert o.shape == w.shape and torch.equal(o.cpu(), w)
+
+
+@pytest.mark.parametrize("layout", ["own", "lightning", "adamw"])
+def test_optimizer_resume_matches_uninterrupted_run(layout):
+    """save -> load -> step == an uninterrupted run (moments, step count for the bias correction, EMA copy), for the optimizer's own
+    state_dict, the reference EMA optimizer's layout written by checkpoint.to_lightning_checkpoint (FiT/ema.py:322-347) and a bare
+    torch.optim.AdamW state (per-parameter 'step' only)."""
+    from fit_b200.checkpoint import to_lightning_checkpoint
+    from fit_b200.optim import FusedAdamWEMA
+    g = torch.Generator().manual_seed(3)
+    shapes = [(40, 24), (17,), (3, 5, 7)]
+    grads = [[torch.randn(s, generator=g).cuda() for s in shapes] for _ in range(5)]
+
+    def make():
+        gg = torch.Generator().manual_seed(9)
+        return [torch.nn.Parameter(torch.randn(s, generator=gg).cuda()) for s in shapes]
+
+    def run(opt, params, steps):
+        for k in steps:
+            for p, gr in zip(params, grads[k]):
+                p.grad = gr.clone()
+            opt.step()
+
+    pa = make(); oa = FusedAdamWEMA(pa, lr=1e-2, ema_decay=0.9)
+    run(oa, pa, range(5))
+    pb = make(); ob = FusedAdamWEMA(pb, lr=1e-2, ema_decay=0.9)
+    run(ob, pb, range(3))
+    if layout == "own":
+        state = ob.state_dict()
+    elif layout == "lightning":
+        mod = torch.nn.Module()
+        for i, p in enumerate(pb):
+            mod.register_parameter(f"p{i}", p)
+        state = to_lightning_checkpoint(mod, "FiT-S/8", optimizer=ob, global_step=3)["optimizer_states"][0]
+    else:
+        state = {"state": {i: {"step": torch.tensor(3.0), "exp_avg": m.clone(), "exp_avg_sq": v.clone()}
+                           for i, (m, v) in enumerate(zip(ob.exp_avg, ob.exp_avg_sq))},
+                 "param_groups": [{"lr": 1e-2, "betas": (0.9, 0.999), "eps": 1e-8, "weight_decay": 0.0, "params": [0, 1, 2]}]}
+    pc = [torch.nn.Parameter(p.detach().clone()) for p in pb]
+    oc = FusedAdamWEMA(pc, lr=1e-2, ema_decay=0.9)
+    if layout == "adamw":           # a bare AdamW state carries no EMA: continue from the interrupted run's copy
+        for e, src in zip(oc.ema_params, ob.ema_params):
+            e.copy_(src)
+    oc.load_state_dict(state)
+    assert oc.step_count == 3
+    run(oc, pc, range(3, 5))
+    for a, c in zip(pa, pc):
+        assert torch.equal(a.detach(), c.detach())
+    for a, c in zip(oa.ema_params, oc.ema_params):
+        assert torch.equal(a, c)

@@ -42,6 +42,38 @@ def _grad_sync_worker(rank, world, port, q):
         gs.on_grads("x", {"t": t})
         gs.finish()
         ok = ok and torch.equal(t, torch.ones(4) * (rank + 1))
+    # gradient accumulation (accumulate_grad_batches=2, FiT/train.py:288): micro-step 1 under no_sync accumulates locally into p.grad
+    # (autograd's job), micro-step 2 is synced -> every rank must end with mean_over_ranks(g1 + g2) in p.grad, identical on all ranks
+    class _M(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.w = torch.nn.Parameter(torch.zeros(6, 3))
+            self.b = torch.nn.Parameter(torch.zeros(5))
+    m = _M()
+    gs.attach(m)
+    g1 = {"w": torch.randn(6, 3, generator=g), "b": torch.randn(5, generator=g)}
+    g2 = {"w": torch.randn(6, 3, generator=g), "b": torch.randn(5, generator=g)}
+    want = {}
+    for n in g1:
+        both = [torch.zeros_like(g1[n]) for _ in range(world)]
+        dist.all_gather(both, g1[n] + g2[n])
+        want[n] = sum(both) / world
+
+    def autograd_accumulate(grads):          # what autograd does with the tensors backward() returns
+        for n, prm in m.named_parameters():
+            prm.grad = grads[n].clone() if prm.grad is None else prm.grad + grads[n]
+    with gs.no_sync():
+        gs.on_grads("all", {n: t.clone() for n, t in g1.items()})
+        gs.finish()
+        autograd_accumulate(g1)
+    new = {n: t.clone() for n, t in g2.items()}
+    flat = torch.cat([new["w"].reshape(-1), new["b"].reshape(-1)])           # in-place bucket, as the training engine allocates them
+    views = {"w": flat[:18].view(6, 3), "b": flat[18:]}
+    gs.on_grads("all", views, flat)
+    gs.finish()
+    autograd_accumulate(views)
+    for n, prm in m.named_parameters():
+        ok = ok and torch.allclose(prm.grad, want[n], atol=1e-6)
     q.put((rank, ok))
     dist.destroy_process_group()
 
