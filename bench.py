@@ -123,20 +123,62 @@ def cpu_reference_run(model_name: str, images: int, steps: int, warmup: int):
     return images / (STEPS_PER_IMAGE * s_step), s_step, {"cores": torch.get_num_threads(), "images": images, "steps": steps}
 
 
+def cpu_unmodified_reference_run(model_name: str, images: int, steps: int, warmup: int):
+    """Same sample as cpu_reference_run, but through the UNMODIFIED reference modules (FiT.forward_with_cfg + SpacedDiffusion.p_sample,
+    sample_lightning.py:36-70) imported from /root/reference (build container only: the GPU box has no /root/reference).
+    Returns None when the reference tree is absent."""
+    if not os.path.isdir("/root/reference/FiT"):
+        return None
+    import torch
+    from oracle import fit_oracle as fo
+    from oracle.make_goldens import import_reference
+    torch.set_num_threads(os.cpu_count() or 1)
+    FiT, FiT_models, create_diffusion, precompute = import_reference()
+    cfg = fo.model_config(model_name)
+    model = FiT_models[model_name]()
+    model.load_state_dict(fo.random_state_dict(cfg, seed=0))
+    model.eval()
+    diffusion = create_diffusion(str(STEPS_PER_IMAGE))
+    d = cfg["hidden_size"] // cfg["num_heads"]
+    g = torch.Generator().manual_seed(123)
+    z = torch.randn(images, 4, 32, 32, generator=g)
+    x = torch.cat([z, z], 0)
+    y = torch.cat([torch.randint(0, 1000, (images,), generator=g), torch.full((images,), 1000)])
+    pos = torch.tensor(precompute(d, 16, 16, max_length=256), dtype=torch.float32)[None]
+    mask = torch.ones(2 * images, 256, dtype=torch.bool)
+    kw = dict(y=y, pos=pos, mask=mask, cfg_scale=1.5)
+    times = []
+    with torch.no_grad():
+        for k in range(warmup + steps):
+            i = STEPS_PER_IMAGE - 1 - k
+            t0 = time.perf_counter()
+            t = torch.full((2 * images,), i, dtype=torch.long)
+            x = diffusion.p_sample(model.forward_with_cfg, x, t, clip_denoised=False, model_kwargs=kw)["sample"]
+            if k >= warmup:
+                times.append(time.perf_counter() - t0)
+    s_step = sum(times) / len(times)
+    return images / (STEPS_PER_IMAGE * s_step), s_step, {"cores": torch.get_num_threads(), "images": images, "steps": steps}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     steps = max(1, min(args.steps, 4))
     warm = 1 if args.warmup > 0 else 0
-    val, s_step, info = cpu_reference_run(args.model, images=2, steps=steps, warmup=warm)
+    kind = "reference"
+    res = cpu_unmodified_reference_run(args.model, images=2, steps=steps, warmup=warm)
+    if res is None:   # GPU box: /root/reference does not exist there -> the pinned restatement
+        kind = "port"
+        res = cpu_reference_run(args.model, images=2, steps=steps, warmup=warm)
+    val, s_step, info = res
     sample = (f"{info['images']} images ({2 * info['images']} rows with CFG) x {steps} of the 250 denoising steps, fp32, "
               f"{info['cores']} threads; img/s = images / (250 x s/step)")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "images/sec", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
             "ms_per_step": s_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.model} 256x256 (32x32x4 latent, 256 tokens), 250-step DDPM p_sample, CFG 1.5; CPU sample of the same step",
                        "steps_per_image": STEPS_PER_IMAGE},
-            "cpu_baseline": {"value": val, "unit": "images/sec", "cores": info["cores"], "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "images/sec", "cores": info["cores"], "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -150,6 +192,14 @@ def randomize_zero_init(model, seed=1):
     for name, p in model.named_parameters():
         if "adaLN_modulation" in name or name.startswith("final_layer.linear") or name.endswith(".bias"):
             p.data.copy_(torch.randn(p.shape, generator=g) * 0.02)
+
+
+def traffic_tag():
+    """Newest committed `ncu --set full` summary of the block kernels (profiles/<tag>_ncu_full_block_kernels.csv); its header line names the
+    git revision it was captured from."""
+    import glob
+    tags = sorted(os.path.basename(f).split("_ncu_full")[0] for f in glob.glob(os.path.join(ROOT, "profiles", "*_ncu_full_block_kernels.csv")))
+    return tags[-1] if tags else "none"
 
 
 def ncu_traffic(tag="r1f"):
@@ -181,8 +231,8 @@ def ncu_traffic(tag="r1f"):
 
 
 def time_kernel(fn, iters, flush):
-    """(best, mean) seconds over `iters` launches, each after an L2 flush, CUDA events on the launch stream.  The roofline uses the BEST
-    launch: MEASURED_PEAKS.json's burst peaks are best-of-10 figures, so numerator and denominator are taken the same way."""
+    """(best, mean) seconds over `iters` launches, each after an L2 flush, CUDA events on the launch stream.  The roofline's `achieved` /
+    `frac` use the MEAN launch (`*_best` alongside: MEASURED_PEAKS.json's burst peaks are best-of-10 figures)."""
     import torch
     fn(); fn()
     torch.cuda.synchronize()
@@ -218,13 +268,15 @@ def kernel_rooflines(model, sampler, peaks, iters=10):
     res = {}
 
     def add(name, fn, flops, bytes_):
-        t, t_mean = time_kernel(fn, iters, flush)
+        t_best, t = time_kernel(fn, iters, flush)
         tf, gbs = flops / t / 1e12, bytes_ / t / 1e9
         tensor_bound = flops / (peaks["tf_burst"] * 1e12) >= bytes_ / (peaks["hbm_gbs"] * 1e9)
-        res[name] = {"bound": "tensor" if tensor_bound else "hbm", "ms": t * 1e3, "ms_mean": t_mean * 1e3,
-                     "achieved": tf if tensor_bound else gbs, "peak": peaks["tf_burst"] if tensor_bound else peaks["hbm_gbs"],
-                     "unit": "TFLOP/s" if tensor_bound else "GB/s",
-                     "frac": (tf / peaks["tf_burst"]) if tensor_bound else (gbs / peaks["hbm_gbs"]), "traffic": None}
+        peak = peaks["tf_burst"] if tensor_bound else peaks["hbm_gbs"]
+        ach = tf if tensor_bound else gbs
+        res[name] = {"bound": "tensor" if tensor_bound else "hbm", "ms": t * 1e3, "ms_best": t_best * 1e3,
+                     "achieved": ach, "achieved_best": ach * t / t_best, "peak": peak, "unit": "TFLOP/s" if tensor_bound else "GB/s",
+                     "frac": ach / peak, "frac_best": ach * t / t_best / peak, "timing": "mean of %d launches (best alongside)" % iters,
+                     "algorithmic_bytes": bytes_, "algorithmic_flops": flops, "traffic": None}
 
     add("gemm_tc[swiglu fc1_g|fc1_x]", lambda: ops.gemm(ws.h, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU),
         2.0 * M * D * 2 * Hp, (M * D + 2 * Hp * D + M * Hp) * 2)
@@ -241,11 +293,179 @@ def kernel_rooflines(model, sampler, peaks, iters=10):
     nel = sampler.x.numel()
     add("cfg_ddpm_step", lambda: ops.cfg_step(sampler.x, sampler.raw, sampler.noise, sampler.t_idx[: sampler.B], tb["coef"], cfg_pairs=sampler.B,
                                               cfg_scale=1.5, sample=sampler.x), 0.0, nel * 4 * 5)
-    for k, b in ncu_traffic().items():
+    # family (3) kernels (north_star: "HBM GB/s of the elementwise and step kernels"): µs-scale, launch-latency bound at this size
+    R = 2 * sampler.B
+    p_, Cin = model.patch_size, model.in_channels
+    add("embed_tokens", lambda: ops.embed_tokens(sampler.x, W.x_w, W.x_b, ws.xs, R, T, p_, Cin), 0.0, sampler.x.numel() * 4 + M * D * bpe)
+    fsh, fsc = ws.fin_views
+    add("final_layer", lambda: ops.final_layer(ws.xs, fsh, fsc, W.n_mod, W.fin_w, W.fin_b, sampler.raw, R, T, p_, model.out_channels), 0.0,
+        M * D * bpe + sampler.raw.numel() * 4)
+    add("philox_normal", lambda: ops.philox_normal(sampler.noise, 1234, sampler.t_idx, sampler.row_offset_dev), 0.0, sampler.noise.numel() * 4)
+    tag = traffic_tag()
+    for k, b in ncu_traffic(tag).items():
         if k in res:
             res[k]["traffic"] = b
-            res[k]["traffic_source"] = "profiles/r1f_ncu_full_block_kernels.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+            res[k]["traffic_source"] = f"profiles/{tag}_ncu_full_block_kernels.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
     return res
+
+
+# ------------------------------------------------------------------------------------------------ extra workloads (BASELINE configs 3-4)
+def strong_scaling_run(model, diffusion, args, world, rank, dev, pos, barrier, all_max):
+    """BASELINE config 3 as written: global batch `--batch` SHARDED over the GPUs (batch/world images per GPU, no collective).
+    Returns images/sec of the whole job (same metric as the headline line, fixed total work)."""
+    import torch
+    from fit_b200.sampler import CFGSampler, shard_rows
+    b0, b1 = shard_rows(args.batch, world, rank)
+    Bs = b1 - b0
+    g = torch.Generator().manual_seed(2000 + rank)
+    z = torch.randn(Bs, 4, 32, 32, generator=g).pin_memory()
+    y = torch.randint(0, 1000, (Bs,), generator=g).pin_memory()
+    smp = CFGSampler(model, diffusion, batch=Bs, latent_hw=(32, 32), cfg_scale=1.5, seed=1234, row_offset=b0)
+    smp.load(z, y, pos)
+    smp.run(max(args.warmup, 1))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    smp.run(args.steps)
+    e1.record()
+    barrier()
+    ms = all_max(e0.elapsed_time(e1)) / args.steps
+    del smp
+    return {"img_s": args.batch / (STEPS_PER_IMAGE * ms * 1e-3), "ms_per_step": ms, "per_gpu_batch": Bs, "global_batch": args.batch,
+            "token_rows_per_gpu": 2 * Bs * 256}
+
+
+def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters=5):
+    """BASELINE config 4: FiT-XL/2 bf16 training step, `samples` synthetic latents per GPU (global batch 256 at 8 GPUs), forward + hand-written
+    backward + per-block NCCL gradient all-reduce (GradSync, overlapped on a side stream) + fused AdamW/EMA (FiT/train.py:45-69,215-217,283-291).
+    Timed with CUDA events, max over ranks.  Also timed: the same step with the exchange switched off (local gradients only) and the
+    all-reduce of the same buckets alone, which give the exposed / hidden share of the collective."""
+    import torch
+    import torch.distributed as dist
+    from fit_b200 import _lib as L
+    from fit_b200.optim import FusedAdamWEMA
+    from fit_b200.train import GradSync, masked_mse_loss
+    from fit_b200.rope import precompute_freqs_cis_2d
+    D, Hd, Ld, heads = MODELS[args.model]
+    T, d = 256, D // heads
+    was_training = model.training
+    model.train()
+    g = torch.Generator().manual_seed(300 + rank)
+    x = torch.randn(samples, T, 16, generator=g).to(dev)
+    tgt = torch.randn(samples, T, 16, generator=g).to(dev)
+    t = torch.randint(0, 1000, (samples,), generator=g).to(dev)
+    y = torch.randint(0, 1000, (samples,), generator=g).to(dev)
+    pos = torch.tensor(precompute_freqs_cis_2d(d, 16, 16, max_length=256), dtype=torch.float32)[None].expand(samples, T, d).contiguous().to(dev)
+    mask = torch.ones(samples, T, dtype=torch.bool, device=dev)
+    sync = GradSync().attach(model) if world > 1 else None
+    opt = FusedAdamWEMA(model.parameters(), lr=1e-4, weight_decay=0.0, ema_decay=0.9999)
+
+    def step(do_opt=True):
+        for p in model.parameters():
+            p.grad = None
+        out = model(x, t, y, pos, mask, train=True)
+        loss = masked_mse_loss(out, tgt, mask)
+        loss.backward()          # GradSync.finish runs inside the autograd node's backward
+        if do_opt:
+            opt.step()
+        return loss
+
+    def timed(fn, n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        return all_max(e0.elapsed_time(e1)) / n
+
+    for _ in range(2):
+        loss = step()
+    ms = timed(step, iters)
+    res = {"train_step_ms": ms, "samples_per_gpu": samples, "global_batch": samples * world,
+           "train_samples_s": samples * world / (ms * 1e-3),
+           "train_tflops_per_gpu": 3 * samples * forward_flops(D, Hd, Ld, T) / (ms * 1e-3) / 1e12,
+           "train_loss": float(loss.detach()),
+           "train_step": "fwd + bwd + per-block NCCL all-reduce (AVG, fp32, overlapped) + fused AdamW/EMA; 3 x forward FLOPs counted"}
+    if sync is not None:
+        with sync.no_sync():
+            ms_local = timed(step, iters)
+        # the same buckets, all-reduced alone (nothing to overlap with)
+        names = [n for n, _ in model.named_parameters()]
+        sizes = {}
+        for n, p in model.named_parameters():
+            key = n.split(".")[1] if n.startswith("blocks.") else "rest"
+            sizes[key] = sizes.get(key, 0) + p.numel()
+        bufs = [torch.zeros(v, dtype=torch.float32, device=dev) for v in sizes.values()]
+        def ar_alone():
+            for b in bufs:
+                dist.all_reduce(b, op=dist.ReduceOp.AVG)
+        ar_alone()
+        ms_ar = timed(ar_alone, 3)
+        exposed = max(ms - ms_local, 0.0)
+        res.update({"train_step_local_ms": ms_local, "allreduce_alone_ms": ms_ar, "allreduce_exposed_ms": exposed,
+                    "allreduce_overlap_frac": max(0.0, 1.0 - exposed / ms_ar) if ms_ar > 0 else None,
+                    "allreduce_bytes": 4 * sum(sizes.values()), "allreduce_buckets": len(bufs), "collective": "ncclAllReduce (AVG, fp32)"})
+        object.__setattr__(model, "_grad_sync", None)
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        L.check(L.lib().fitb200_set_sm_limit(n_sm), "set_sm_limit")   # GradSync reserved SMs for NCCL: give them back
+    del opt
+    for p in model.parameters():
+        p.grad = None
+    model.train(was_training)
+    object.__setattr__(model, "_train_engine", None)
+    torch.cuda.empty_cache()
+    return res
+
+
+def eager_torch_run(model, args, dev, pos, steps=2):
+    """The same-box bar: the reference's arithmetic as eager PyTorch (cuBLAS / ATen kernels) on THIS GPU at the headline shape -- the pinned
+    restatement oracle/fit_oracle.py + diffusion_oracle.p_sample (checker code used as a timed baseline, like cpu_baseline), fp32 with TF32
+    matmuls (torch.set_float32_matmul_precision('high'), FiT/train.py:28) and under bf16 autocast."""
+    import torch
+    from oracle import diffusion_oracle as do
+    from oracle import fit_oracle as fo
+    cfg = fo.model_config(args.model)
+    sd = {k: v.detach() for k, v in model.state_dict().items()}
+    B = args.batch
+    tb, tmap = do.create(str(STEPS_PER_IMAGE))
+    g = torch.Generator().manual_seed(5)
+    z = torch.randn(B, 4, 32, 32, generator=g).to(dev)
+    y = torch.cat([torch.randint(0, 1000, (B,), generator=g), torch.full((B,), 1000)]).to(dev)
+    mask = torch.ones(2 * B, 256, dtype=torch.bool, device=dev)
+    posd = pos.to(dev)
+    tmap_t = torch.as_tensor(tmap).to(dev)
+    out = {}
+    old = torch.get_float32_matmul_precision()
+    torch.set_float32_matmul_precision("high")
+    try:
+        for name, ctx in (("tf32", None), ("bf16_autocast", torch.autocast("cuda", dtype=torch.bfloat16))):
+            x = torch.cat([z, z], 0)
+            ts = []
+            with torch.no_grad():
+                for k in range(1 + steps):
+                    i = STEPS_PER_IMAGE - 1 - k
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    t = torch.full((2 * B,), i, dtype=torch.long, device=dev)
+                    if ctx is None:
+                        eps = fo.forward_with_cfg(sd, cfg, x, tmap_t[t], y, posd, mask, 1.5)
+                    else:
+                        with ctx:
+                            eps = fo.forward_with_cfg(sd, cfg, x, tmap_t[t], y, posd, mask, 1.5)
+                    x = do.p_sample(tb, x, t, eps.float(), torch.randn_like(x))["sample"]
+                    e1.record()
+                    torch.cuda.synchronize()
+                    if k >= 1:
+                        ts.append(e0.elapsed_time(e1))
+            ms = sum(ts) / len(ts)
+            out[name] = {"img_s": B / (STEPS_PER_IMAGE * ms * 1e-3), "ms_per_step": ms}
+            del x, eps
+            torch.cuda.empty_cache()
+    finally:
+        torch.set_float32_matmul_precision(old)
+    return out
 
 
 def run_cuda_arm(args):
@@ -262,6 +482,7 @@ def run_cuda_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("FITB200_DDP_RESERVE_SMS", "8"))   # the DDP leg: NCCL stays inside the SMs GradSync leaves free
         # NCCL prints its version banner on STDOUT when the communicator is created (NCCL_DEBUG >= VERSION on the GPU boxes; WARN still
         # prints it).  stdout carries exactly one JSON line, so file descriptor 1 points at stderr while the communicator comes up.
         sys.stdout.flush()
@@ -326,6 +547,25 @@ def run_cuda_arm(args):
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms, e2e_ms = float(tms[0]), float(tms[1])
     assert bool(torch.isfinite(out_host).all()), "non-finite latents"
+
+    def all_max(v):
+        tv = torch.tensor([v], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tv, op=dist.ReduceOp.MAX)
+        return float(tv[0])
+
+    extra = {}
+    if not args.no_extras:
+        # ---- config 3 as written (strong scaling: the global batch sharded) and config 4 (DDP training step) -- all ranks take part
+        if world > 1:
+            extra["strong"] = strong_scaling_run(model, diffusion, args, world, rank, dev, pos, barrier, all_max)
+        else:
+            extra["strong"] = {"img_s": world * B / (STEPS_PER_IMAGE * ms / args.steps * 1e-3), "ms_per_step": ms / args.steps, "per_gpu_batch": B,
+                               "global_batch": B, "token_rows_per_gpu": 2 * B * 256, "note": "N = 1: identical to the headline run"}
+        extra["strong_img_s"] = extra["strong"]["img_s"]
+        extra["train"] = train_run(model, args, world, rank, dev, barrier, all_max)
+        extra["train_step_ms"] = extra["train"]["train_step_ms"]
+        barrier()
     if rank == 0:
         ms_step = ms / args.steps
         value = world * B / (STEPS_PER_IMAGE * ms_step * 1e-3)
@@ -336,6 +576,11 @@ def run_cuda_arm(args):
         roof = dict(dom, kernel="gemm_tc_kernel<256, SWIGLU> (fc1_g|fc1_x, M=%d K=%d N=%d)" % (2 * B * 256, D, 2 * Hd), peak_source=peaks["source"],
                     whole_step_tflops=value / world * flops_img / 1e12, whole_step_frac_of_sustained=value / world * flops_img / 1e12 / peaks["tf_sustained"],
                     kernels=kr)
+        if not args.no_extras:
+            eg = eager_torch_run(model, args, dev, pos)
+            extra["torch_eager_b200"] = eg
+            extra["torch_eager_b200_img_s"] = eg["bf16_autocast"]["img_s"]
+            extra["torch_eager_b200_tf32_img_s"] = eg["tf32"]["img_s"]
         cpu = None
         if not args.no_cpu_baseline:
             cv, cs, info = cpu_reference_run(args.model, images=1, steps=2, warmup=1)
@@ -354,7 +599,7 @@ def run_cuda_arm(args):
                 "e2e": {"value": e2e_val, "unit": "images/sec", "h2d_bytes_per_step": (z_host.numel() * 4 + y_host.numel() * 8 + pos.numel() * 4) / args.steps,
                         "d2h_bytes_per_step": out_host.numel() * 4 / args.steps,
                         "note": "CFGSampler.load (pinned host latents/labels/RoPE table -> device) + K graph-replayed steps + device -> pinned host copy of the latents"},
-                "roofline": roof, "cpu_baseline": cpu}
+                "roofline": roof, "cpu_baseline": cpu, "extra": extra}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -373,6 +618,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="images per GPU")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the strong-scaling, training-step and eager-torch side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -87,7 +87,7 @@ def create(timestep_respacing, diffusion_steps: int = 1000):
 
 def _gather(arr: np.ndarray, t: Tensor, ndim: int) -> Tensor:
     """_extract_into_tensor: float64 table -> .float() per-row scalar -- gaussian_diffusion.py:882-894."""
-    v = torch.from_numpy(arr)[t.long()].float()
+    v = torch.from_numpy(arr).to(t.device)[t.long()].float()   # the reference copies the table to the timestep's device per call
     return v.reshape(-1, *([1] * (ndim - 1)))
 
 

@@ -101,7 +101,7 @@ def layer_norm(x: Tensor) -> Tensor:
 def timestep_embedding(t: Tensor, dim: int = 256, max_period: float = 10000.0) -> Tensor:
     """[cos(t f) | sin(t f)], f_i = exp(-ln(max_period) i/half) -- FiT/models/fit.py:61-80."""
     half = dim // 2
-    f = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32) / half)
+    f = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32) / half).to(t.device)   # host table moved to t.device (fit.py:73-75)
     a = t.to(torch.float32)[:, None] * f[None, :]
     return torch.cat([a.cos(), a.sin()], dim=1)
 

@@ -274,8 +274,8 @@ def test_submodule_forwards_match_oracle(precision, tol):
         x = x.bfloat16().float()
     with torch.no_grad():
         want_blk = fo.block_forward(sd, 1, x, c, mask, pos, cfg["num_heads"])
-        want_att = fo.self_attention(sd, "blocks.0.attn.", x, mask, pos, cfg["num_heads"])
-        want_ffn = fo.swiglu(sd, "blocks.1.ffn.", x)
+        want_att = fo.self_attention(sd, "blocks.0.", x, mask, pos, cfg["num_heads"])
+        want_ffn = fo.swiglu(sd, "blocks.1.", x)
         want_fin = fo.final_layer(sd, x, c)
         xc, cc, mc, pc = x.cuda(), c.cuda(), mask.cuda(), pos.cuda()
         got_blk = model.blocks[1](xc, cc, mc, freqs_cis=pc)
@@ -337,4 +337,8 @@ def test_cfg_sampler_needs_null_class_row_and_eval_mode_grads():
     assert out.requires_grad
     masked_mse_loss(out, target.cuda(), mask.cuda()).backward()
     z = golden("fit_tiny_d64")
-    assert rel_l2(model.blocks[0].attn.qkv.weight.grad, z["g.blocks.0.attn.qkv.weight"]) < 1e-3
+    got, ref = model.blocks[0].attn.qkv.weight.grad, torch.tensor(z["g.blocks.0.attn.qkv.weight"])
+    if tuple(ref.shape) != tuple(got.shape):     # the golden keeps 2048 evenly spaced entries of large gradients (make_goldens.sample_flat)
+        f = got.reshape(-1)
+        got = f[:: max(1, f.numel() // 2048)][:2048]
+    assert rel_l2(got, ref) < 1e-3
