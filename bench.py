@@ -218,8 +218,9 @@ def ncu_traffic(tag="r1f"):
     for r in rows[1:]:
         name, b = r[0], float(r[ir]) * scale(hdr[ir]) + float(r[iw]) * scale(hdr[iw])
         key = None
-        if name.startswith("gemm_tc_kernel<256, 3"): key = "gemm_tc[swiglu fc1_g|fc1_x]"
-        elif name.startswith("gemm_tc_kernel<256, 4"): key = "gemm_tc[qkv+rope]"
+        lna = name.rstrip().endswith("1, 1>")   # LN-prologue instantiations
+        if name.startswith("gemm_tc_kernel<256, 3"): key = "gemm_tc[ln+swiglu fc1_g|fc1_x]" if lna else "gemm_tc[swiglu fc1_g|fc1_x]"
+        elif name.startswith("gemm_tc_kernel<256, 4"): key = "gemm_tc[ln+qkv+rope]" if lna else "gemm_tc[qkv+rope]"
         elif name.startswith("gemm_tc_kernel<256, 2"):
             key = "gemm_tc[proj+gate+resid]" if gate_seen == 0 else "gemm_tc[fc2+gate+resid]"
             gate_seen += 1
@@ -278,17 +279,34 @@ def kernel_rooflines(model, sampler, peaks, iters=10):
                      "frac": ach / peak, "frac_best": ach * t / t_best / peak, "timing": "mean of %d launches (best alongside)" % iters,
                      "algorithmic_bytes": bytes_, "algorithmic_flops": flops, "traffic": None}
 
-    add("gemm_tc[swiglu fc1_g|fc1_x]", lambda: ops.gemm(ws.h, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU),
-        2.0 * M * D * 2 * Hp, (M * D + 2 * Hp * D + M * Hp) * 2)
-    add("gemm_tc[qkv+rope]", lambda: ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS_ROPE, rope=sampler.pos, rope_cols=2 * D),
-        2.0 * M * D * 3 * D, (M * D + 3 * D * D + M * 3 * D) * 2)
+    fused = getattr(ws, "modA", None) is not None   # LayerNorm + modulate as the GEMM prologue (FiTEngine.block)
+    R2 = 2 * sampler.B
+    if fused:
+        from fit_b200.engine import LN_EPS
+        ops.row_stats(ws.xs, ws.parts)
+        add("gemm_tc[ln+swiglu fc1_g|fc1_x]", lambda: ops.gemm(ws.xs, e["fc1_w"], None, ws.g, EPI_SWIGLU, rows_per_sample=T,
+                                                              ln=(ws.modA[1, :R2], ws.cf, ws.parts, LN_EPS)),
+            2.0 * M * D * 2 * Hp, (M * D + 2 * Hp * D + M * Hp) * 2)
+        add("gemm_tc[ln+qkv+rope]", lambda: ops.gemm(ws.xs, e["qkv_w"], None, ws.qkv, EPI_BIAS_ROPE, rope=sampler.pos, rope_cols=2 * D, rows_per_sample=T,
+                                                     ln=(ws.modA[0, :R2], ws.cq, ws.parts, LN_EPS)),
+            2.0 * M * D * 3 * D, (M * D + 3 * D * D + M * 3 * D) * 2)
+        add("gemm_tc[ln vectors qkv]", lambda: ops.gemm(ws.modA[0], e["qkv_w"], e["qkv_b"], ws.cq, EPI_BIAS, bias_row0=R2),
+            2.0 * 2 * R2 * D * 3 * D, (2 * R2 * D + 3 * D * D) * 2 + 2 * R2 * 3 * D * 4)
+        add("gemm_tc[ln vectors fc1]", lambda: ops.gemm(ws.modA[1], e["fc1_w"], e["fc1_b"], ws.cf, EPI_BIAS, bias_row0=R2),
+            2.0 * 2 * R2 * D * 2 * Hp, (2 * R2 * D + 2 * Hp * D) * 2 + 2 * R2 * 2 * Hp * 4)
+    else:
+        add("gemm_tc[swiglu fc1_g|fc1_x]", lambda: ops.gemm(ws.h, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU),
+            2.0 * M * D * 2 * Hp, (M * D + 2 * Hp * D + M * Hp) * 2)
+        add("gemm_tc[qkv+rope]", lambda: ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS_ROPE, rope=sampler.pos, rope_cols=2 * D),
+            2.0 * M * D * 3 * D, (M * D + 3 * D * D + M * 3 * D) * 2)
     add("gemm_tc[fc2+gate+resid]", lambda: ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=W.n_mod,
                                                      rows_per_sample=T, resid=ws.xs), 2.0 * M * Hp * D, (M * Hp + D * Hp) * 2 + 2 * M * D * bpe)
     add("gemm_tc[proj+gate+resid]", lambda: ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=W.n_mod,
                                                       rows_per_sample=T, resid=ws.xs), 2.0 * M * D * D, (M * D + D * D) * 2 + 2 * M * D * bpe)
     add("attn_tc[softmax(qk^T)v]", lambda: ops.attention(ws.qkv, None, ws.kv_len, sampler.mask, 2 * sampler.B, T, h, dh, ws.att, prerotated=True),
         4.0 * (2 * sampler.B) * T * T * D, (M * 3 * D + M * D) * 2)
-    add("ln_modulate", lambda: ops.ln_modulate(ws.xs, sh1, sc1, W.n_mod, T, ws.h), 0.0, M * D * (bpe + 2))
+    if not fused:
+        add("ln_modulate", lambda: ops.ln_modulate(ws.xs, sh1, sc1, W.n_mod, T, ws.h), 0.0, M * D * (bpe + 2))
     tb = sampler.diffusion._tables(sampler.device)
     nel = sampler.x.numel()
     add("cfg_ddpm_step", lambda: ops.cfg_step(sampler.x, sampler.raw, sampler.noise, sampler.t_idx[: sampler.B], tb["coef"], cfg_pairs=sampler.B,
@@ -572,8 +590,10 @@ def run_cuda_arm(args):
         e2e_val = world * B / (STEPS_PER_IMAGE * (e2e_ms / args.steps) * 1e-3)
         flops_img = 2 * STEPS_PER_IMAGE * forward_flops(D, Hd, L, 256)
         kr = kernel_rooflines(model, sampler, peaks)
-        dom = kr["gemm_tc[swiglu fc1_g|fc1_x]"]
-        roof = dict(dom, kernel="gemm_tc_kernel<256, SWIGLU> (fc1_g|fc1_x, M=%d K=%d N=%d)" % (2 * B * 256, D, 2 * Hd), peak_source=peaks["source"],
+        dom_key = "gemm_tc[ln+swiglu fc1_g|fc1_x]" if "gemm_tc[ln+swiglu fc1_g|fc1_x]" in kr else "gemm_tc[swiglu fc1_g|fc1_x]"
+        dom = kr[dom_key]
+        roof = dict(dom, kernel="gemm_tc_kernel<256, SWIGLU%s> (fc1_g|fc1_x, M=%d K=%d N=%d)" % (", LN prologue" if "ln+" in dom_key else "", 2 * B * 256, D, 2 * Hd),
+                    peak_source=peaks["source"],
                     whole_step_tflops=value / world * flops_img / 1e12, whole_step_frac_of_sustained=value / world * flops_img / 1e12 / peaks["tf_sustained"],
                     kernels=kr)
         if not args.no_extras:

@@ -36,6 +36,11 @@ class GemmArgs(C.Structure):
         ("rope_freqs", C.c_void_p), ("rope_rows", C.c_int32), ("rope_tokens", C.c_int32), ("rope_head_dim", C.c_int32),
         ("rope_cols", C.c_int32),
         ("a_mn", C.c_int32), ("b_mn", C.c_int32),
+        ("bias_row0", C.c_int32),
+        ("ln_g", C.c_void_p), ("ld_ln_g", C.c_int64),
+        ("ln_c", C.c_void_p), ("ln_samples", C.c_int32),
+        ("ln_parts", C.c_void_p), ("ln_nparts", C.c_int32), ("ln_eps", C.c_float),
+        ("stats_out", C.c_void_p),
     ]
 
 

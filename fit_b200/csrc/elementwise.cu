@@ -533,6 +533,48 @@ static void launch_ln(const void* x, int M, int D, int rows_per_sample, const fl
 
 using namespace fitb200;
 
+// ---------------------------------------------------------------------------------------------
+// pieces of the GEMM LayerNorm + modulate prologue (gemm_tc.cu, LNA)
+// ---------------------------------------------------------------------------------------------
+// parts[m] = (sum_k x[m,k], sum_k x[m,k]^2): one warp per row (the rows the embedder wrote; every later residual stream gets its sums from
+// the GATE_RESID GEMM epilogue)
+template <typename InT>
+__global__ void __launch_bounds__(256) row_stats_kernel(const InT* __restrict__ x, int M, int D, float2* __restrict__ parts, int nparts) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= M) return;
+  const InT* xr = x + (size_t)row * D;
+  float s1 = 0.f, s2 = 0.f;
+  for (int v = lane; v < (D >> 3); v += 32) {
+    const Vec8<InT> a = Vec8<InT>::load(xr + v * 8);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { s1 += a.v[e]; s2 = fmaf(a.v[e], a.v[e], s2); }
+  }
+  s1 = warp_sum(s1); s2 = warp_sum(s2);
+  if (lane < nparts) parts[(size_t)row * nparts + lane] = lane == 0 ? make_float2(s1, s2) : make_float2(0.f, 0.f);
+}
+
+// out[set][s][k] = bf16(1 + scale_set[s,k]),  out[set][S + s][k] = bf16(shift_set[s,k])
+__global__ void __launch_bounds__(256) modulation_pack_kernel(const float* __restrict__ shift, const float* __restrict__ scale, long ld_mod, int S, int D,
+                                                           int n_sets, long set_stride, __nv_bfloat16* __restrict__ out) {
+  const int dv = D >> 2;
+  const long total = (long)n_sets * 2 * S * dv;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % dv);
+    long r = i / dv;
+    const int s2 = (int)(r % (2 * S));
+    const int set = (int)(r / (2 * S));
+    const bool is_shift = s2 >= S;
+    const int smp = is_shift ? s2 - S : s2;
+    const float* src = (is_shift ? shift : scale) + (size_t)smp * ld_mod + set * set_stride + v * 4;
+    float4 f = *reinterpret_cast<const float4*>(src);
+    if (!is_shift) { f.x += 1.0f; f.y += 1.0f; f.z += 1.0f; f.w += 1.0f; }
+    uint2 o;
+    o.x = pack_bf16x2(f.x, f.y); o.y = pack_bf16x2(f.z, f.w);
+    *reinterpret_cast<uint2*>(out + ((size_t)set * 2 * S + s2) * D + v * 4) = o;
+  }
+}
+
 extern "C" {
 
 const char* fitb200_last_error(void) { return g_err; }
@@ -694,6 +736,26 @@ int fitb200_add_i64(int64_t* idx, int n, int64_t delta, fitb200_stream_t stream)
   FITB200_CHECK_ARG(idx && n > 0, "add_i64: bad arguments");
   add_i64_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(idx, n, delta);
   FITB200_CHECK_LAUNCH("add_i64");
+  return FITB200_OK;
+}
+
+int fitb200_row_stats(const void* x, int x_dtype, int M, int D, float* parts, int nparts, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && parts && M > 0 && D > 0 && D % 8 == 0 && nparts >= 1 && nparts <= 32 && ((uintptr_t)parts & 7) == 0, "row_stats: bad arguments");
+  FITB200_DISPATCH_ACT(x_dtype, InT, {
+    row_stats_kernel<InT><<<(unsigned)ceil_div(M, 8), 256, 0, (cudaStream_t)stream>>>((const InT*)x, M, D, (float2*)parts, nparts);
+  })
+  FITB200_CHECK_LAUNCH("row_stats");
+  return FITB200_OK;
+}
+
+int fitb200_modulation_pack(const float* shift, const float* scale, int64_t ld_mod, int S, int D, int n_sets, int64_t set_stride, void* out,
+                            fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(shift && scale && out && S > 0 && D > 0 && n_sets > 0, "modulation_pack: bad arguments");
+  FITB200_CHECK_ARG(D % 4 == 0 && ld_mod % 4 == 0 && set_stride % 4 == 0 && ((uintptr_t)shift & 15) == 0 && ((uintptr_t)scale & 15) == 0 && ((uintptr_t)out & 7) == 0,
+                    "modulation_pack: D, ld_mod, set_stride must be multiples of 4 and the tables 16-byte aligned");
+  const long total = (long)n_sets * 2 * S * (D / 4);
+  modulation_pack_kernel<<<step_grid(total), 256, 0, (cudaStream_t)stream>>>(shift, scale, ld_mod, S, D, n_sets, set_stride, (__nv_bfloat16*)out);
+  FITB200_CHECK_LAUNCH("modulation_pack");
   return FITB200_OK;
 }
 

@@ -22,6 +22,14 @@ namespace fitb200 {
 constexpr int GT_BM = 128, GT_BK = 64;
 constexpr int GT_THREADS = 320;  // producer + mma + 8 epilogue warps
 constexpr int GT_EPI_THREADS = 256;  // two warps per TMEM lane quarter: each takes half of a slab's columns
+// LNA kernels (LayerNorm + adaLN modulate prologue): 20 warps in five warpgroups, so that setmaxnreg can move registers between the roles --
+//   warps 0..3   TMA producer (B), MMA issuer, relay thread (publishes the A rows to the tensor core), one idle warp      32 registers
+//   warps 4..11  epilogue                                                                                                  144 registers
+//   warps 12..19 A producers: two warps per scheduler (one warp each was issue-latency bound: 805 clk per k-slab),         96 registers
+//                three k-slabs of 4 rows x 16 bytes in flight per thread
+constexpr int GT_LNA_THREADS = 256;
+constexpr int GT_THREADS_LNA = 640;
+constexpr int GT_LNA_ROWS = 128 / (GT_LNA_THREADS / 8);   // rows per producer thread
 constexpr int GT_SLAB_BYTES = GT_BM * 128;  // 128 rows x 128 bytes
 constexpr int GT_ROPE_MAX_HD = 72;          // head dims up to this keep the tile's RoPE rows in shared memory (FiT: 64, 72)
 constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - 256 /*barriers*/;
@@ -29,14 +37,16 @@ constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - 256 /*barriers*/;
 // PAIR: two CTAs of a cluster (one TPC) share one 256 x BN tile through tcgen05 cta_group::2 -- each CTA stages its own 128 rows of A
 // and HALF of the B rows, so the shared-memory bytes read per MMA flop drop by a third (a 128 x 192 single-CTA tile needs 106 of the
 // SM's 128 B/clk; the pair needs 75) and each CTA's ring holds more stages.
-template <int BN, int EPI, bool PAIR = false> struct GtCfg {
+template <int BN, int EPI, bool PAIR = false, bool LNA = false> struct GtCfg {
   static constexpr int A_BYTES = GT_BM * GT_BK * 2;
   static constexpr int BNL = PAIR ? BN / 2 : BN;  // B rows staged by this CTA
   static constexpr int B_BYTES = BNL * GT_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // out x2 (+ resid x2) (+ the RoPE table rows of the tile's 128 tokens, fp32, row stride head_dim + 4 words: conflict-free float4 reads)
   static constexpr int ROPE_BYTES = EPI == FITB200_EPI_BIAS_ROPE ? GT_BM * (GT_ROPE_MAX_HD + 4) * 4 : 0;
-  static constexpr int EPI_BYTES = (EPI == FITB200_EPI_BIAS_GATE_RESID ? 4 : 2) * GT_SLAB_BYTES + ROPE_BYTES;
+  // LNA: the (c1, c2) vectors of the tile's sample and columns, one copy per epilogue lane quarter: [4][2][BN] fp32
+  static constexpr int LNC_BYTES = LNA ? 4 * 2 * BN * 4 : 0;
+  static constexpr int EPI_BYTES = (EPI == FITB200_EPI_BIAS_GATE_RESID ? 4 : 2) * GT_SLAB_BYTES + ROPE_BYTES + LNC_BYTES;
   static constexpr int STAGES_RAW = (GT_SMEM_BUDGET - EPI_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > (PAIR ? 8 : 6) ? (PAIR ? 8 : 6) : STAGES_RAW;
   static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;  // 2 accumulator stages, power of two
@@ -51,6 +61,15 @@ struct GtParams {
   const float* gate; long ld_gate; int rows_per_sample;
   const float* rope_freqs; int rope_rows, rope_tokens, rope_hd, rope_cols;
   int tail_rows;  // K-major B: rows of the narrower TMA box (tmBt) used for the last, cut column tile (0 = always the full box)
+  int bias_row0;  // the bias is added to rows >= bias_row0 only (0 = every row)
+  // LNA (LayerNorm + adaLN-modulate prologue, see the A-producer warps below)
+  const __nv_bfloat16* lnx; long ld_lnx;   // raw residual-stream rows x [M, K]
+  const __nv_bfloat16* lng; long ld_lng;   // bf16(1 + scale) [samples, K]
+  const float* lnc; int ln_samples;        // [2 * samples, N]: c1[s, n] = sum_k bf16(1+scale[s,k]) W[n,k], then c2[s, n] = bias[n] + sum_k bf16(shift[s,k]) W[n,k]
+  const float2* ln_parts; int ln_nparts;   // [M, nparts] partial (sum x, sum x^2) of every row of x
+  float ln_eps;
+  // GATE_RESID: partial row sums of the OUTPUT rows (the next LayerNorm's statistics), [M, 2 * column tiles] (nullable)
+  float2* stats_out; int stats_nparts;
   int dbg;  // FITB200_GEMM_DBG=1: epilogue releases the accumulator without reading it (mainloop ceiling measurement only)
 };
 
@@ -64,12 +83,20 @@ __device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
 // OutT = bf16: a slab is 64 output columns; OutT = float: 32 output columns (both 128 bytes per row).
 // AMN / BMN: the operand is stored contraction-major ([K, M] resp. [K, N] row-major: the dgrad / wgrad GEMMs of the backward pass);
 // its k-slab is fetched as 64-column TMA boxes and read through MN-major SWIZZLE_128B descriptors (tools/probe/umma_probe_mn.cu).
-template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false>
-__global__ void __launch_bounds__(GT_THREADS, 1)
+//
+// LNA: the A operand is modulate(LayerNorm(x), shift, scale) (fit.py:45-46,303,308,332,336) of the raw residual stream x, formed inside this kernel
+// instead of by a separate pass over HBM.  With g = 1 + scale[s], mu / rstd the row statistics:
+//     sum_k ((x - mu) rstd g_k + shift_k) W[n,k]  =  rstd (sum_k (x g_k) W[n,k]  -  mu c1[s,n])  +  c2[s,n]
+// so the only per-element work on the operand path is ONE packed bf16 multiply x * bf16(g_k): four extra warps load x from global memory
+// (16-byte loads, two k-slabs ahead), multiply, and store into the 128B-swizzled A ring the MMA reads (no extra shared-memory traffic:
+// the store replaces TMA's); mu, rstd, c1, c2 are applied to the fp32 accumulators in the epilogue.  c1 / c2 are [samples, N] vectors
+// from a small GEMM of the modulation rows with the same weight; the row sums come from the GATE_RESID epilogue that wrote x.
+template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false, bool LNA = false>
+__global__ void __launch_bounds__(LNA ? GT_THREADS_LNA : GT_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmBt,
                const GtParams p) {
-  using Cfg = GtCfg<BN, EPI, PAIR>;
+  using Cfg = GtCfg<BN, EPI, PAIR, LNA>;
   static_assert(!PAIR || !BMN || Cfg::BNL % 64 == 0, "pair tiles with a contraction-major B: whole 64-column boxes per CTA");
   constexpr int STAGES = Cfg::STAGES;
   constexpr int TM = PAIR ? 2 * GT_BM : GT_BM;  // rows of one scheduled tile (both CTAs of a pair)
@@ -82,6 +109,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int NSLAB = BN / ACCC;
   constexpr int CW = 16 / (int)sizeof(OutT);          // output columns per 16-byte chunk: 8 (bf16) or 4 (fp32)
   static_assert(BN % ACCC == 0, "tile width must be a whole number of slabs");
+  static_assert(!LNA || (PAIR && !AMN && !BMN && sizeof(OutT) == 2 && (ROPE || SWIGLU || EPI == FITB200_EPI_BIAS)), "LNA: K-major pair tiles, bf16 output");
+  constexpr int LNA_WARPS = GT_LNA_THREADS / 32;
+  constexpr int EPI_WARP0 = LNA ? 4 : 2;          // first epilogue warp (a multiple of 4 apart from the TMEM lane quarter rule: quarter = warp % 4)
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
@@ -91,6 +121,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* smemOut = smem + STAGES * Cfg::STAGE_BYTES;          // [2][128 rows][128 B]
   uint8_t* smemRes = smemOut + 2 * GT_SLAB_BYTES;               // [2][128 rows][128 B]  (RESID only)
   float* smemRope = reinterpret_cast<float*>(smemOut + 2 * GT_SLAB_BYTES);  // [128 rows][head_dim + 4]  (ROPE only)
+  float* smemLnc = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES - Cfg::LNC_BYTES);  // [4][2][BN]  (LNA only)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
   uint64_t* full_bar = bars;                     // [STAGES]  TMA -> MMA
   uint64_t* empty_bar = bars + STAGES;           // [STAGES]  MMA -> TMA
@@ -98,6 +129,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       epilogue -> MMA
   uint64_t* res_bar = bars + 2 * STAGES + 4;     // [4][2]    residual slab rows of lane quarter q landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
+  uint64_t* abar = bars + 2 * STAGES + 13;       // [STAGES]  LNA: A-producer warps -> relay thread
+  static_assert(!LNA || 3 * STAGES + 13 <= 32, "barrier area is 256 bytes");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_n = ceil_div(p.N, BN), tiles_m = ceil_div(p.M, TM);
@@ -114,7 +147,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ptx::prefetch_tmap(&tmOut);
     if (RESID) ptx::prefetch_tmap(&tmRes);
     if (p.tail_rows > 0) ptx::prefetch_tmap(&tmBt);
-    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
+    // LNA: a slot is full once the B bytes have landed AND the relay thread of each CTA of the pair has published the A rows of its producers
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], LNA ? 1 + (PAIR ? 2 : 1) : 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+      if (LNA) ptx::mbar_init(&abar[s], LNA_WARPS);
+    }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
       ptx::mbar_init(&tempty_bar[s], PAIR ? 2 * (GT_EPI_THREADS / 32) : GT_EPI_THREADS);  // pair: one arrival per epilogue warp of both CTAs
@@ -131,8 +169,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-
+  // LNA: registers follow the work -- every warp of a warpgroup executes the same setmaxnreg, first thing in its role branch
   if (warp == 0) {
+    if (LNA) ptx::setmaxnreg_dec<32>();
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
@@ -146,10 +185,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // both CTAs' bytes are counted on the LEADER's full barrier (the only one the MMA thread waits on)
             // the cut last column tile fetches only the B rows its MMAs read: a full box would make that tile as expensive as a whole one
             const bool tail = !BMN && nn < BN && p.tail_rows > 0;
-            const uint32_t stage_bytes = tail ? Cfg::A_BYTES + p.tail_rows * 128 : Cfg::STAGE_BYTES;
+            const uint32_t stage_bytes = (LNA ? 0 : Cfg::A_BYTES) + (tail ? p.tail_rows * 128 : Cfg::B_BYTES);
             if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * stage_bytes);
             const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
-            if (AMN) {
+            if (LNA) {
+              // A is written by the A-producer warps
+            } else if (AMN) {
 #pragma unroll
               for (int b = 0; b < GT_BM / 64; ++b) ptx::tma_load_2d_pair(smemA + stage * Cfg::A_BYTES + b * 8192, &tmA, fb, m0 + b * 64, kb * GT_BK);
             } else {
@@ -184,6 +225,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else if (warp == 1) {
+    if (LNA) ptx::setmaxnreg_dec<32>();
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0 && rank == 0) {
       constexpr uint32_t idesc0 = ptx::idesc_bf16_f32(TM, 0) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
@@ -201,6 +243,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int nn = min(BN, (p.N - (tile % tiles_n) * BN + NGRAN - 1) / NGRAN * NGRAN);
         const uint32_t idesc = idesc0 | ((uint32_t)(nn >> 3) << 17);
         for (int kb = 0; kb < num_kb; ++kb) {
+          // (LNA: the A rows of both CTAs were published by their relay threads behind a generic -> async proxy fence.  NOT a cluster-scope
+          // acquire here: it compiles to CCTL.IVALL -- an L1 invalidate per k-slab, which turned every spill reload and table read of the
+          // other warps into an L2 round trip: the fused GEMMs ran 2.5x slower)
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
           const uint32_t a_addr = ptx::smem_u32(smemA + stage * Cfg::A_BYTES), b_addr = ptx::smem_u32(smemB + stage * Cfg::B_BYTES);
@@ -221,10 +266,109 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
     __syncwarp();
+  } else if (LNA && warp == 2) {
+    ptx::setmaxnreg_dec<32>();
+    // ------------------------------------------------------------------ relay thread (LNA): A rows stored -> proxy fence -> MMA's full barrier
+    if (lane == 0) {
+      const uint32_t full_leader = PAIR ? ptx::mapa(ptx::smem_u32(&full_bar[0]), 0) : ptx::smem_u32(&full_bar[0]);
+      const int my_tiles = wid < num_tiles ? (num_tiles - 1 - wid) / nwork + 1 : 0;
+      const int total = my_tiles * num_kb;
+      int stage = 0; uint32_t phase = 0;
+      for (int i = 0; i < total; ++i) {
+        ptx::mbar_wait(&abar[stage], phase);    // acquire: the four producer warps' st.shared of this slot
+        ptx::fence_proxy_async_smem();          // ... become visible to the async proxy
+        if (PAIR) ptx::mbar_arrive_remote(full_leader + stage * 8); else ptx::mbar_arrive(&full_bar[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (LNA && warp == 3) {
+    ptx::setmaxnreg_dec<32>();  // idle: fills the first warpgroup
+  } else if (LNA && warp >= EPI_WARP0 + GT_EPI_THREADS / 32) {
+    // ------------------------------------------------------------------ A-producer warps (LNA): x * bf16(1 + scale) -> swizzled A ring
+    // thread = (16-byte chunk c of the 128-byte k-slab row, row group rg): rows rg, rg + 16, ... rg + 112 of this CTA's 128 rows.  One warp
+    // instruction reads 4 rows x 128 contiguous bytes and stores 512 contiguous (chunk-permuted) bytes: coalesced and conflict-free.
+    ptx::setmaxnreg_dec<96>();   // (no change: the launch allocates 96 per thread)
+    constexpr int NR = GT_LNA_ROWS, RSTEP = GT_LNA_THREADS / 8;   // rows per thread, row distance between them
+    const int pt = (int)threadIdx.x - (EPI_WARP0 * 32 + GT_EPI_THREADS);
+    const int c = pt & 7, rg = pt >> 3;
+    // (rg + 32 j) & 7 == rg & 7: the swizzle phase is per thread.  All shared-memory addresses are 32-bit shared-window addresses so that the
+    // loop below issues few instructions per k-slab (the first version spent ~300 on 64-bit address arithmetic and was issue-bound)
+    const uint32_t dst0 = ptx::smem_u32(smemA) + (uint32_t)(rg * 128 + ((c ^ (rg & 7)) << 4));
+    const uint32_t empty0 = ptx::smem_u32(&empty_bar[0]), abar0 = ptx::smem_u32(&abar[0]);
+    const int my_tiles = wid < num_tiles ? (num_tiles - 1 - wid) / nwork + 1 : 0;
+    const int total = my_tiles * num_kb;
+    // fetch cursor (three k-slabs ahead of the store cursor) and its per-tile state: byte pointer to (first row of this thread, its chunk),
+    // byte offsets of its rows from there (rows beyond M repeat the last existing one: their output rows are clipped by the store), the
+    // modulation row.  rows_per_sample % 128 == 0 (checked on the host): the 128 rows of a CTA tile belong to one sample, so one 16-byte load
+    // of bf16(1 + scale) per thread and k-slab serves all its rows; each chunk is read once per CTA and tile (an L2 hit, never an L1 hit), so
+    // it is prefetched with the rows.
+    int f_it = 0, f_kb = 0;
+    const char* xbase = nullptr;
+    const char* gbase = nullptr;
+    uint32_t roff[NR];
+    const uint32_t rstride = (uint32_t)(RSTEP * p.ld_lnx * 2);
+    auto enter_tile = [&]() {
+      const int m0 = ((wid + f_it * nwork) / tiles_n) * TM + row_off;
+      const int r0 = min(m0 + rg, p.M - 1);
+      xbase = reinterpret_cast<const char*>(p.lnx + (size_t)r0 * p.ld_lnx + c * 8);
+      const int jmax = min(NR - 1, (p.M - 1 - r0) / RSTEP);
+#pragma unroll
+      for (int j = 0; j < NR; ++j) roff[j] = (uint32_t)min(j, jmax) * rstride;
+      gbase = reinterpret_cast<const char*>(p.lng + (size_t)(min(m0, p.M - 1) / p.rows_per_sample) * p.ld_lng + c * 8);
+    };
+    if (total > 0) enter_tile();
+    auto fetch = [&](uint4 (&b)[NR], uint4& g) {   // K % 64 == 0 (checked on the host): every k-slab is whole
+      const uint32_t kb2 = (uint32_t)f_kb * (GT_BK * 2);
+      const char* xk = xbase + kb2;
+#pragma unroll
+      for (int j = 0; j < NR; ++j) b[j] = __ldg(reinterpret_cast<const uint4*>(xk + roff[j]));
+      g = __ldg(reinterpret_cast<const uint4*>(gbase + kb2));
+      if (++f_kb == num_kb) { f_kb = 0; ++f_it; if (f_it < my_tiles) enter_tile(); }
+    };
+    int stage = 0; uint32_t phase = 0;
+    auto store = [&](uint4 (&b)[NR], const uint4& g) {
+      ptx::mbar_wait_addr(empty0 + stage * 8, phase ^ 1);   // the MMAs that read this slot (of both CTAs) have retired
+      const uint32_t dst = dst0 + stage * Cfg::A_BYTES;
+      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&g);
+#pragma unroll
+      for (int j = 0; j < NR; ++j) {
+        uint4 v = b[j];
+        __nv_bfloat162* v2 = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v2[e] = __hmul2(v2[e], g2[e]);
+        ptx::st_shared_v4(dst + j * RSTEP * 128, v);
+      }
+      // hand the rows to the relay thread with a plain CTA-scope arrive.  The generic -> async proxy fence the tensor core's operand reads need
+      // is NOT executed here: it compiles to MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC, and a MEMBAR waits for every load the thread has in flight
+      // -- the prefetched k-slabs.  The relay thread has no loads in flight.
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_addr(abar0 + stage * 8);
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    };
+    // three register buffers: the loads of a k-slab are in flight for three slab periods (~1500 clk) before their values are needed
+    const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+    uint4 b0[NR], b1[NR], b2[NR], g0 = z4, g1 = z4, g2 = z4;
+    if (total > 0) fetch(b0, g0);
+    if (total > 1) fetch(b1, g1);
+    if (total > 2) fetch(b2, g2);
+    for (int i = 0; i < total; i += 3) {
+      store(b0, g0);
+      if (i + 3 < total) fetch(b0, g0);
+      if (i + 1 < total) {
+        store(b1, g1);
+        if (i + 4 < total) fetch(b1, g1);
+      }
+      if (i + 2 < total) {
+        store(b2, g2);
+        if (i + 5 < total) fetch(b2, g2);
+      }
+    }
   } else {
-    // ------------------------------------------------------------------ epilogue warps (2..5)
+    // ------------------------------------------------------------------ epilogue warps (2..9)
+    if (LNA) ptx::setmaxnreg_inc<128>();
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
-    const int half = (warp - 2) >> 2;        // which half of each slab's columns this warp handles
+    const int half = (warp - EPI_WARP0) >> 2;  // which half of each slab's columns this warp handles
     const int row = quarter * 32 + lane;     // row inside the tile == TMEM lane
     // The epilogue is four independent pipelines, one per TMEM lane quarter (two warps = 64 threads, 32 tile rows): each stages, stores
     // and prefetches the residual of ITS rows (32-row TMA boxes) behind its own named barrier, so a slow quarter never stalls the others
@@ -256,6 +400,34 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int m = min(m0 + row, p.M - 1);
       const float* gate_row = nullptr;
       if (RESID) gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
+      float st1 = 0.f, st2 = 0.f;  // RESID: sum / sum of squares of this row's output columns handled by this thread (stats_out)
+      // LNA: value = ln_a * acc + (ln_b * c1[s, n] + c2[s, n]) with ln_a = rstd, ln_b = -mean * rstd of this row of x
+      float ln_a = 1.f, ln_b = 0.f;
+      const float* c1row = nullptr;
+      const float* c2row = nullptr;
+      if (LNA) {
+        float s1 = 0.f, s2 = 0.f;
+        const float2* pp = p.ln_parts + (size_t)m * p.ln_nparts;
+        for (int i = 0; i < p.ln_nparts; ++i) { const float2 t = __ldg(pp + i); s1 += t.x; s2 += t.y; }
+        const float mu = s1 / (float)p.K;
+        const float var = fmaxf(s2 / (float)p.K - mu * mu, 0.f);
+        ln_a = 1.0f / sqrtf(var + p.ln_eps);
+        ln_b = -mu * ln_a;
+        // c1 / c2 of this tile's sample (one per CTA tile: rows_per_sample % 128 == 0) and columns -> this quarter's shared-memory copy, loaded
+        // BEFORE the accumulator wait: they differ from tile to tile, so reading them from global memory at their point of use was an L2 round
+        // trip per 16-byte chunk (the fused GEMMs ran 2.5x slower, epilogue-bound).  The quarter's threads are past the last named barrier of
+        // the previous tile (all its reads of the copy), and slab 0's first named barrier below publishes the new one.
+        float* lc = smemLnc + quarter * 2 * BN;
+        const float* src = p.lnc + (size_t)(min(m0, p.M - 1) / p.rows_per_sample) * p.N + n0;
+        const size_t c2off = (size_t)p.ln_samples * p.N;
+        for (int i = half * 32 + lane; i < BN; i += 64) {
+          const bool in = n0 + i < p.N;
+          lc[i] = in ? __ldg(src + i) : 0.f;
+          lc[BN + i] = in ? __ldg(src + c2off + i) : 0.f;
+        }
+        c1row = lc - n0;          // indexed by the global column like the bias
+        c2row = lc + BN - n0;
+      }
       const float* rope_row = nullptr;  // (cos, sin) pairs of this row's token
       if (ROPE) {
         if (p.rope_hd <= GT_ROPE_MAX_HD) {
@@ -337,23 +509,43 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const int nb = nacc + half * HACC + a0;
               const bool ok = nb < p.N;
               const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-              const float4 g0 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb)) : z4;
-              const float4 g1 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb + 4)) : z4;
-              const float4 u0 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb + 16)) : z4;
-              const float4 u1 = ok ? __ldg(reinterpret_cast<const float4*>(p.bias + nb + 20)) : z4;
-              const float bg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-              const float bu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+              const float* brow = LNA ? c2row : p.bias;   // LNA: c2 carries the bias (shared-memory copy: plain loads)
+              auto ld4 = [&](const float* q) { return LNA ? *reinterpret_cast<const float4*>(q) : __ldg(reinterpret_cast<const float4*>(q)); };
+              const float4 g0 = ok ? ld4(brow + nb) : z4;
+              const float4 g1 = ok ? ld4(brow + nb + 4) : z4;
+              const float4 u0 = ok ? ld4(brow + nb + 16) : z4;
+              const float4 u1 = ok ? ld4(brow + nb + 20) : z4;
+              float bg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+              float bu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+              if (LNA) {
+                const float4 h0 = ok ? ld4(c1row + nb) : z4;
+                const float4 h1 = ok ? ld4(c1row + nb + 4) : z4;
+                const float4 w0 = ok ? ld4(c1row + nb + 16) : z4;
+                const float4 w1 = ok ? ld4(c1row + nb + 20) : z4;
+                const float cg[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+                const float cu[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
 #pragma unroll
-              for (int i = 0; i < 8; ++i) v[i] = silu_f(acc[a0 + i] + bg[i]) * (acc[a0 + 16 + i] + bu[i]);
+                for (int i = 0; i < 8; ++i) { bg[i] = fmaf(ln_b, cg[i], bg[i]); bu[i] = fmaf(ln_b, cu[i], bu[i]); }
+              }
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[i] = silu_f(fmaf(ln_a, acc[a0 + i], bg[i])) * fmaf(ln_a, acc[a0 + 16 + i], bu[i]);
             } else {
               const int nb = nacc + j * CW;
               const bool ok = nb < p.N;
 #pragma unroll
               for (int i4 = 0; i4 < CW / 4; ++i4) {
                 float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (p.bias && ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + nb + i4 * 4));
-                v[i4 * 4 + 0] = acc[jj * CW + i4 * 4 + 0] + b4.x; v[i4 * 4 + 1] = acc[jj * CW + i4 * 4 + 1] + b4.y;
-                v[i4 * 4 + 2] = acc[jj * CW + i4 * 4 + 2] + b4.z; v[i4 * 4 + 3] = acc[jj * CW + i4 * 4 + 3] + b4.w;
+                if (LNA) {
+                  if (ok) {
+                    const float4 c1 = *reinterpret_cast<const float4*>(c1row + nb + i4 * 4);
+                    b4 = *reinterpret_cast<const float4*>(c2row + nb + i4 * 4);
+                    b4.x = fmaf(ln_b, c1.x, b4.x); b4.y = fmaf(ln_b, c1.y, b4.y); b4.z = fmaf(ln_b, c1.z, b4.z); b4.w = fmaf(ln_b, c1.w, b4.w);
+                  }
+                } else if (p.bias && ok && m >= p.bias_row0) {
+                  b4 = __ldg(reinterpret_cast<const float4*>(p.bias + nb + i4 * 4));
+                }
+                v[i4 * 4 + 0] = fmaf(ln_a, acc[jj * CW + i4 * 4 + 0], b4.x); v[i4 * 4 + 1] = fmaf(ln_a, acc[jj * CW + i4 * 4 + 1], b4.y);
+                v[i4 * 4 + 2] = fmaf(ln_a, acc[jj * CW + i4 * 4 + 2], b4.z); v[i4 * 4 + 3] = fmaf(ln_a, acc[jj * CW + i4 * 4 + 3], b4.w);
               }
               if (ROPE) {  // complex_mult (fit.py:152-154): (a + ib)(c + id), pairs (2j, 2j+1); identity (1, 0) on the v columns
 #pragma unroll
@@ -384,6 +576,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   v[i4 * 4 + 0] = fmaf(g4.x, v[i4 * 4 + 0], r[i4 * 4 + 0]); v[i4 * 4 + 1] = fmaf(g4.y, v[i4 * 4 + 1], r[i4 * 4 + 1]);
                   v[i4 * 4 + 2] = fmaf(g4.z, v[i4 * 4 + 2], r[i4 * 4 + 2]); v[i4 * 4 + 3] = fmaf(g4.w, v[i4 * 4 + 3], r[i4 * 4 + 3]);
                 }
+                if (ok) {  // row statistics of the new residual stream: the LayerNorm that follows never re-reads x for them
+#pragma unroll
+                  for (int i = 0; i < CW; ++i) { st1 += v[i]; st2 = fmaf(v[i], v[i], st2); }
+                }
               }
             }
             uint4 o;
@@ -395,6 +591,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             *reinterpret_cast<uint4*>(obuf + ((j ^ sw) << 4)) = o;
           }
         }
+        if (RESID && slab == NSLAB - 1 && p.stats_out && m0 + row < p.M)
+          p.stats_out[(size_t)(m0 + row) * p.stats_nparts + (tile % tiles_n) * 2 + half] = make_float2(st1, st2);
         if (slab == NSLAB - 1) {  // accumulator fully read: hand the TMEM stage back to the MMA warp
           ptx::tc_fence_before();
           if (PAIR) {
@@ -461,9 +659,9 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int dtype, long rows, long
   return FITB200_OK;
 }
 
-template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false>
+template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false, bool LNA = false>
 static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
-  using Cfg = GtCfg<BN, EPI, PAIR>;
+  using Cfg = GtCfg<BN, EPI, PAIR, LNA>;
   CUtensorMap tmA, tmB, tmOut, tmRes, tmBt;
   int rc = AMN ? make_tmap(&tmA, a.A, FITB200_BF16, a.K, a.M, a.lda, GT_BK, 64) : make_tmap(&tmA, a.A, FITB200_BF16, a.M, a.K, a.lda, GT_BM, GT_BK);
   if (rc) return rc;
@@ -501,7 +699,14 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   p.dbg = 0;
 #endif
   p.tail_rows = tail_rows;
-  auto kern = gemm_tc_kernel<BN, EPI, OutT, AMN, BMN, PAIR>;
+  p.bias_row0 = a.bias_row0;
+  p.lnx = (const __nv_bfloat16*)a.A; p.ld_lnx = a.lda;
+  p.lng = (const __nv_bfloat16*)a.ln_g; p.ld_lng = a.ld_ln_g;
+  p.lnc = a.ln_c; p.ln_samples = a.ln_samples;
+  p.ln_parts = (const float2*)a.ln_parts; p.ln_nparts = a.ln_nparts; p.ln_eps = a.ln_eps;
+  p.stats_out = (float2*)a.stats_out; p.stats_nparts = 2 * ceil_div(a.N, BN);
+  constexpr int THREADS = LNA ? GT_THREADS_LNA : GT_THREADS;
+  auto kern = gemm_tc_kernel<BN, EPI, OutT, AMN, BMN, PAIR, LNA>;
   static bool attr_done = false;  // per template instantiation
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -512,7 +717,7 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
     const int tiles = ceil_div(a.M, 2 * GT_BM) * ceil_div(a.N, BN);
     const int pairs = tiles < sm_count() / 2 ? tiles : sm_count() / 2;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(GT_THREADS); cfg.dynamicSmemBytes = Cfg::SMEM_BYTES; cfg.stream = s;
+    cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = Cfg::SMEM_BYTES; cfg.stream = s;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
@@ -523,7 +728,7 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
   }
   const int tiles = ceil_div(a.M, GT_BM) * ceil_div(a.N, BN);
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  kern<<<grid, GT_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmOut, tmRes, tmBt, p);
+  kern<<<grid, THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmOut, tmRes, tmBt, p);
   FITB200_CHECK_LAUNCH("gemm_bf16_tc");
   return FITB200_OK;
 }
@@ -544,6 +749,19 @@ static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
   }
   // K-major operands: CTA pairs (256 x BN tiles, cta_group::2) whenever there are at least two row blocks; FITB200_GEMM_PAIR=0 forces single-CTA tiles
   static const bool pair_ok = [] { const char* e = getenv("FITB200_GEMM_PAIR"); return !(e && e[0] == '0'); }();
+  if (a.ln_g) {  // LayerNorm + modulate prologue: 256-wide pair tiles, bf16 output
+    if constexpr (BN == 256 && sizeof(OutT) == 2) {
+      if (a.M > GT_BM) {
+        switch (a.epilogue) {
+          case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, false, true, true>(a, s);
+          case FITB200_EPI_BIAS_ROPE: return launch_tc<BN, FITB200_EPI_BIAS_ROPE, OutT, false, false, true, true>(a, s);
+          case FITB200_EPI_SWIGLU: return launch_tc<BN, FITB200_EPI_SWIGLU, OutT, false, false, true, true>(a, s);
+        }
+      }
+    }
+    set_last_error("gemm_bf16_tc: the LN prologue needs M > 128, N > 128, bf16 output and a BIAS / BIAS_ROPE / SWIGLU epilogue");
+    return FITB200_ERR_UNSUPPORTED;
+  }
   if (pair_ok && a.M > GT_BM) {
     switch (a.epilogue) {
       case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, false, true>(a, s);
@@ -594,7 +812,7 @@ extern "C" int fitb200_gemm_bf16_tc(const fitb200_gemm_args* ap, fitb200_stream_
   FITB200_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.B & 15) == 0 && ((uintptr_t)a.out & 15) == 0, "gemm_bf16_tc: A, B, out must be 16-byte aligned");
   FITB200_CHECK_ARG(a.N % 8 == 0 && a.ldo % 8 == 0, "gemm_bf16_tc: N and ldo must be multiples of 8 (N=%d)", a.N);
   FITB200_CHECK_ARG(a.bias == nullptr || ((uintptr_t)a.bias & 15) == 0, "gemm_bf16_tc: bias must be 16-byte aligned");
-  if (a.epilogue == FITB200_EPI_SWIGLU) FITB200_CHECK_ARG(a.N % 32 == 0 && a.bias, "gemm_bf16_tc: SWIGLU needs N %% 32 == 0 and a packed bias");
+  if (a.epilogue == FITB200_EPI_SWIGLU) FITB200_CHECK_ARG(a.N % 32 == 0 && (a.bias || a.ln_g), "gemm_bf16_tc: SWIGLU needs N %% 32 == 0 and a packed bias");
   if (a.epilogue == FITB200_EPI_BIAS_ROPE)
     FITB200_CHECK_ARG(a.rope_freqs && ((uintptr_t)a.rope_freqs & 15) == 0 && a.rope_tokens > 0 && a.rope_head_dim > 0 && a.rope_head_dim % 8 == 0 &&
                           a.rope_cols % a.rope_head_dim == 0 && a.rope_cols <= a.N && (a.rope_rows == 1 || (int64_t)a.rope_rows * a.rope_tokens >= a.M),
@@ -603,8 +821,22 @@ extern "C" int fitb200_gemm_bf16_tc(const fitb200_gemm_args* ap, fitb200_stream_
     FITB200_CHECK_ARG(a.gate && a.resid && a.rows_per_sample > 0 && a.ld_gate % 4 == 0 && a.ld_resid % 8 == 0 &&
                           ((uintptr_t)a.gate & 15) == 0 && ((uintptr_t)a.resid & 15) == 0 && a.resid_dtype == a.out_dtype,
                       "gemm_bf16_tc: GATE_RESID needs 16-byte aligned gate/resid, rows_per_sample, and resid dtype == out dtype");
+  if (a.ln_g)
+    FITB200_CHECK_ARG(!a.a_mn && !a.b_mn && a.ln_c && a.ln_parts && a.ln_nparts > 0 && a.ln_samples > 0 && a.rows_per_sample > 0 && a.ld_ln_g % 8 == 0 &&
+                          ((uintptr_t)a.ln_g & 15) == 0 && ((uintptr_t)a.ln_c & 15) == 0 && ((uintptr_t)a.ln_parts & 7) == 0 &&
+                          (int64_t)a.ln_samples * a.rows_per_sample >= a.M,
+                      "gemm_bf16_tc: LN prologue needs ln_g [samples, K] bf16, ln_c [2 samples, N] fp32, ln_parts [M, nparts] and rows_per_sample");
+  if (a.ln_g) FITB200_CHECK_ARG(a.rows_per_sample % GT_BM == 0 && a.K % GT_BK == 0, "gemm_bf16_tc: LN prologue needs rows_per_sample %% 128 == 0 and K %% 64 == 0 (got %d, %d)", a.rows_per_sample, a.K);
+  if (a.stats_out)
+    FITB200_CHECK_ARG(a.epilogue == FITB200_EPI_BIAS_GATE_RESID && !a.a_mn && !a.b_mn && ((uintptr_t)a.stats_out & 7) == 0, "gemm_bf16_tc: stats_out goes with GATE_RESID");
   if (a.out_dtype == FITB200_BF16) return dispatch_bn<__nv_bfloat16>(a, (cudaStream_t)stream);
   if (a.out_dtype == FITB200_F32) return dispatch_bn<float>(a, (cudaStream_t)stream);
   set_last_error("gemm_bf16_tc: unsupported out dtype %d", a.out_dtype);
   return FITB200_ERR_INVALID_ARG;
+}
+
+extern "C" int fitb200_gemm_stats_parts(int N) {
+  static const int force = [] { const char* e = getenv("FITB200_GEMM_BN"); return e ? atoi(e) : 0; }();
+  const int bn = force ? force : (N <= 128 ? 128 : 256);
+  return 2 * ((N + bn - 1) / bn);
 }

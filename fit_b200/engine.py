@@ -14,6 +14,7 @@ and "fp32" (verification mode: CUDA-core fp32 GEMMs and fp32 activations).
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -93,11 +94,31 @@ class _Weights:
         self.fin_w, self.fin_b = f32(model.final_layer.linear.weight), f32(model.final_layer.linear.bias)
 
 
+LN_EPS = 1e-6  # norm1 / norm2 (fit.py:303,308)
+
+
+def ln_prologue_ok(precision: str, M: int, D: int, T: int) -> bool:
+    """The GEMM LayerNorm + modulate prologue (gemm_tc.cu, LNA) serves the bf16 path when every 128-row CTA tile lies inside one sample
+    (T % 128 == 0: the reference's 256-token sequences and the 1024 / 4096-token extrapolation shapes) and the width is a whole number of
+    64-column k-slabs (every FiT size: 384, 768, 1024, 1152); FITB200_LN_FUSE=0 keeps the stand-alone
+    ln_modulate kernel (A/B measurements, and the path every other shape takes)."""
+    return precision == "bf16" and M > 128 and T % 128 == 0 and D > 128 and D % 64 == 0 and os.environ.get("FITB200_LN_FUSE", "1") != "0"
+
+
 class _Workspace:
     def __init__(self, R: int, T: int, D: int, Hp: int, n_mod: int, act: torch.dtype, device):
         M = R * T
         z = dict(device=device)
         self.R, self.T = R, T
+        L6 = (n_mod - 2 * D) // (6 * D)
+        self.modA = None
+        if ln_prologue_ok("bf16" if act == torch.bfloat16 else "fp32", M, D, T) and L6 > 0:
+            # LN prologue operands: packed modulation rows of every block's norm1 / norm2, the (c1, c2) vectors of the current qkv / fc1 GEMM,
+            # partial row sums of the residual stream
+            self.modA = torch.empty(2 * L6, 2 * R, D, dtype=torch.bfloat16, **z)
+            self.cq = torch.empty(2 * R, 3 * D, dtype=torch.float32, **z)
+            self.cf = torch.empty(2 * R, 2 * Hp, dtype=torch.float32, **z)
+            self.parts = torch.empty(M, ops.gemm_stats_parts(D), 2, dtype=torch.float32, **z)
         self.xs = torch.empty(M, D, dtype=act, **z)
         self.h = torch.empty(M, D, dtype=act, **z)
         self.qkv = torch.empty(M, 3 * D, dtype=act, **z)
@@ -111,7 +132,6 @@ class _Workspace:
         self.silu_c = torch.empty(R, D, dtype=act, **z)
         self.kv_len = torch.empty(R, dtype=torch.int32, **z)
         self.n_valid = torch.empty(R, dtype=torch.int32, **z)
-        L6 = (n_mod - 2 * D) // (6 * D)
         # per-block views into the adaLN table: shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp
         # (chunk order of fit.py:329-330); final layer: shift, scale (dit.py:139)
         self.mod_views = [[self.mod[:, (6 * i + k) * D:(6 * i + k + 1) * D] for k in range(6)] for i in range(L6)]
@@ -164,6 +184,9 @@ class FiTEngine:
         ops.gemm(ws.t1, W.t2_w, W.t2_b, ws.t2, EPI_BIAS)
         ops.cond_combine(ws.t2, y, W.y_table, ws.c, ws.silu_c)
         ops.gemm(ws.silu_c, W.ada_w, W.ada_b, ws.mod, EPI_BIAS)
+        if getattr(ws, "modA", None) is not None:
+            D = self.model.hidden_size
+            ops.modulation_pack(ws.mod, ws.mod[:, D:], ws.mod.stride(0), ws.R, D, ws.modA.shape[0], 3 * D, ws.modA)
 
     def block(self, i: int, ws: _Workspace, W: _Weights, pos: Tensor, mask: Optional[Tensor]):
         """FiTBlock.forward (fit.py:326-337) in place on ws.xs."""
@@ -172,6 +195,20 @@ class FiTEngine:
         e = W.blocks[i]
         sh1, sc1, g1, sh2, sc2, g2 = ws.mod_views[i]
         nm = ws.mod.stride(0)
+        if getattr(ws, "modA", None) is not None:
+            # modulate(norm1(x)) and modulate(norm2(x)) (fit.py:332,336) as the PROLOGUE of the qkv / fc1 GEMMs: the modulated rows never exist
+            # in HBM; the row sums of the residual stream come out of the proj / fc2 epilogues (ws.parts)
+            ops.gemm(ws.modA[2 * i], e["qkv_w"], e["qkv_b"], ws.cq, EPI_BIAS, bias_row0=R)
+            ops.gemm(ws.xs, e["qkv_w"], None, ws.qkv, EPI_BIAS_ROPE, rope=pos, rope_cols=2 * D, rows_per_sample=T,
+                     ln=(ws.modA[2 * i, :R], ws.cq, ws.parts, LN_EPS))
+            ops.attention(ws.qkv, None, ws.kv_len, mask, R, T, m.num_heads, D // m.num_heads, ws.att, prerotated=True)
+            ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=nm, rows_per_sample=T, resid=ws.xs,
+                     stats_out=ws.parts)
+            ops.gemm(ws.modA[2 * i + 1], e["fc1_w"], e["fc1_b"], ws.cf, EPI_BIAS, bias_row0=R)
+            ops.gemm(ws.xs, e["fc1_w"], None, ws.g, EPI_SWIGLU, rows_per_sample=T, ln=(ws.modA[2 * i + 1, :R], ws.cf, ws.parts, LN_EPS))
+            ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=nm, rows_per_sample=T, resid=ws.xs,
+                     stats_out=ws.parts)
+            return
         ops.ln_modulate(ws.xs, sh1, sc1, nm, T, ws.h)
         if self.precision == "bf16":
             # apply_rotary_emb (fit.py:160-174) rides in the qkv GEMM epilogue (fp32 accumulators, q and k columns), so the
@@ -329,6 +366,8 @@ class FiTEngine:
         ops.mask_to_kvlen(mask, ws.kv_len, ws.n_valid)
         ops.embed_tokens(x, W.x_w, W.x_b, ws.xs, R, T, p, C_in)
         self.conditioning(ws, W, t, y)
+        if ws.modA is not None:
+            ops.row_stats(ws.xs, ws.parts)
         if collect is not None:
             collect.append(ws.xs.float().view(R, T, D).clone())
         for i in range(len(m.blocks)):

@@ -65,9 +65,13 @@ def cond_combine(t_emb: Tensor, y: Tensor, table: Tensor, c: Optional[Tensor], s
 def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: int = EPI_BIAS, *, M: Optional[int] = None,
          B2: Optional[Tensor] = None, bias2: Optional[Tensor] = None, gate: Optional[Tensor] = None, ld_gate: int = 0,
          rows_per_sample: int = 1, resid: Optional[Tensor] = None, N: Optional[int] = None,
-         rope: Optional[Tensor] = None, rope_cols: int = 0, a_mn: bool = False, b_mn: bool = False, K: Optional[int] = None):
+         rope: Optional[Tensor] = None, rope_cols: int = 0, a_mn: bool = False, b_mn: bool = False, K: Optional[int] = None,
+         bias_row0: int = 0, ln: Optional[tuple] = None, stats_out: Optional[Tensor] = None):
     """out = epilogue(A @ B^T).  A [M,K] and B [N,K] both fp32 (CUDA-core path) or both bf16 (tcgen05 path).
-    ``gate`` may be a strided view: pass the storage-offset view and its row stride ``ld_gate``."""
+    ``gate`` may be a strided view: pass the storage-offset view and its row stride ``ld_gate``.
+    ``ln`` = (g, c, parts, eps): LayerNorm + adaLN-modulate prologue -- A is the raw residual stream, g bf16 [S, K] = 1 + scale,
+    c fp32 [2S, N] the (c1, c2) vectors, parts fp32 [M, nparts, 2] the partial row sums (fitb200_gemm_args.ln_*); needs rows_per_sample.
+    ``stats_out`` (GATE_RESID): fp32 [M, gemm_stats_parts(N), 2] partial row sums of the output."""
     L.require_cuda(A, B, out)
     a = L.GemmArgs()
     # a_mn / b_mn: the operand is stored contraction-major, [K, M] resp. [K, N] (backward GEMMs)
@@ -90,6 +94,18 @@ def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: in
     if rope is not None:   # EPI_BIAS_ROPE: fp32 table [1|samples, tokens, head_dim]
         assert rope.dtype == torch.float32 and rope.dim() == 3 and rope.is_contiguous()
         a.rope_freqs, a.rope_rows, a.rope_tokens, a.rope_head_dim, a.rope_cols = rope.data_ptr(), rope.shape[0], rope.shape[1], rope.shape[2], rope_cols
+    a.bias_row0 = bias_row0
+    if ln is not None:
+        g, c, parts, eps = ln
+        assert g.dtype == torch.bfloat16 and g.dim() == 2 and g.stride(1) == 1 and g.shape[1] == a.K
+        assert c.dtype == torch.float32 and c.is_contiguous() and c.shape == (2 * g.shape[0], a.N)
+        assert parts.dtype == torch.float32 and parts.is_contiguous() and parts.dim() == 3 and parts.shape[0] >= a.M and parts.shape[2] == 2
+        a.ln_g, a.ld_ln_g = g.data_ptr(), g.stride(0)
+        a.ln_c, a.ln_samples = c.data_ptr(), g.shape[0]
+        a.ln_parts, a.ln_nparts, a.ln_eps = parts.data_ptr(), parts.shape[1], eps
+    if stats_out is not None:
+        assert stats_out.dtype == torch.float32 and stats_out.is_contiguous() and stats_out.shape == (a.M, gemm_stats_parts(a.N), 2)
+        a.stats_out = stats_out.data_ptr()
     if A.dtype == torch.float32 and B.dtype == torch.float32:
         fn, what = L.lib().fitb200_gemm_f32, "gemm_f32"
     elif A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16:
@@ -97,6 +113,28 @@ def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: in
     else:
         raise TypeError(f"fit_b200.gemm: A {A.dtype} / B {B.dtype} must both be fp32 or both bf16")
     L.check(fn(C.byref(a), L.stream_ptr()), what)
+    return out
+
+
+def gemm_stats_parts(N: int) -> int:
+    """Partial sums per row that a GATE_RESID GEMM with N output columns writes through ``stats_out``."""
+    return int(L.lib().fitb200_gemm_stats_parts(N))
+
+
+def row_stats(x: Tensor, parts: Tensor):
+    """parts[m, 0] = (sum x[m], sum x[m]^2), parts[m, 1:] = 0; x [M, D], parts fp32 [M, nparts, 2]."""
+    L.require_cuda(x, parts)
+    M, D = x.shape
+    assert parts.dtype == torch.float32 and parts.is_contiguous() and parts.shape[0] == M and parts.shape[2] == 2
+    L.check(L.lib().fitb200_row_stats(L.ptr(_c(x)), L.dtype_code(x), M, D, L.ptr(parts), parts.shape[1], L.stream_ptr()), "row_stats")
+    return parts
+
+
+def modulation_pack(shift: Tensor, scale: Tensor, ld_mod: int, S: int, D: int, n_sets: int, set_stride: int, out: Tensor):
+    """out[set] = [bf16(1 + scale_set) ; bf16(shift_set)] ([2S, D] each); shift / scale: fp32 views of the adaLN table (row stride ld_mod)."""
+    L.require_cuda(shift, scale, out)
+    assert out.dtype == torch.bfloat16 and out.is_contiguous() and out.numel() == n_sets * 2 * S * D
+    L.check(L.lib().fitb200_modulation_pack(L.ptr(shift), L.ptr(scale), ld_mod, S, D, n_sets, set_stride, L.ptr(out), L.stream_ptr()), "modulation_pack")
     return out
 
 

@@ -73,9 +73,13 @@ class CFGSampler:
         ops.add_i64(self.t_idx, -1)
 
     def kernels_per_step(self) -> int:
-        """Number of libfit_b200 kernel launches in one step (7 per block + embed/conditioning/final + 5 loop kernels)."""
+        """Number of libfit_b200 kernel launches in one step: 7 per block (un-fused: 2 ln_modulate + 4 GEMMs + attention; LN prologue: 2 small
+        c-vector GEMMs + 4 GEMMs + attention) + embed / conditioning / final (8) + 4 loop kernels, + modulation_pack and row_stats when the
+        LayerNorm prologue is active."""
+        from .engine import ln_prologue_ok
         L = len(self.model.blocks)
-        return 7 * L + 8 + 4
+        fused = ln_prologue_ok(self.model.engine.precision, 2 * self.B * self.T, self.model.hidden_size, self.T) and L > 0
+        return 7 * L + 8 + 4 + (2 if fused else 0)
 
     def noise_for_step(self, i: int, row_offset: int = 0, rows: Optional[int] = None) -> Tensor:
         rows = self.B if rows is None else rows

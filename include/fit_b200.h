@@ -95,7 +95,26 @@ typedef struct {
    *   wgrad  dW[N,K'] = dY[M,N]^T X[M,K'] : A = dY with a_mn = 1, B = X with b_mn = 1 (contraction over the token rows)
    * FITB200_EPI_BIAS (bias may be NULL) only. */
   int32_t a_mn, b_mn;
+  int32_t bias_row0;               /* bf16 GEMM: the bias is added to rows m >= bias_row0 only (0 = all rows) */
+  /* ---- LayerNorm + adaLN-modulate PROLOGUE (bf16 tcgen05 GEMM; epilogue BIAS, BIAS_ROPE or SWIGLU; M > 128, N > 128) ----
+   * ln_g != NULL: A is the raw residual stream x [M,K] and the GEMM computes  epilogue( modulate(LayerNorm_eps(x), shift, scale) . B^T + bias )
+   * (fit.py:45-46,303,308,332,336: norm1/norm2 without affine, eps 1e-6) without materialising the modulated rows:
+   *     rstd_m * ( sum_k (x[m,k] * g[s,k]) B[n,k]  -  mean_m * c1[s,n] )  +  c2[s,n],      s = m / rows_per_sample
+   *   ln_g     bf16 [ln_samples, K] (row stride ld_ln_g):  g = bf16(1 + scale)
+   *   ln_c     fp32 [2 * ln_samples, N]:  rows [0, S): c1[s,n] = sum_k g[s,k] B[n,k];  rows [S, 2S): c2[s,n] = bias[n] + sum_k bf16(shift[s,k]) B[n,k]
+   *            (fitb200_modulation_pack + one FITB200_EPI_BIAS GEMM of the packed rows with the same B, bias_row0 = S; `bias` is ignored here)
+   *   ln_parts fp32 [M, ln_nparts, 2]: partial (sum x, sum x^2) of every row (summed in order; from stats_out of the GEMM that wrote x, or
+   *            fitb200_row_stats);  ln_eps: the LayerNorm epsilon. */
+  const void* ln_g; int64_t ld_ln_g;
+  const float* ln_c; int32_t ln_samples;
+  const float* ln_parts; int32_t ln_nparts; float ln_eps;
+  /* GATE_RESID (bf16 GEMM): optional fp32 [M, fitb200_gemm_stats_parts(N), 2] partial (sum, sum of squares) of every OUTPUT row -- the
+   * statistics of the LayerNorm that follows (fit.py:332,336), so that nothing re-reads the residual stream for them. */
+  float* stats_out;
 } fitb200_gemm_args;
+
+/* number of partial sums per row written through stats_out for an N-column output */
+int fitb200_gemm_stats_parts(int N);
 
 /* fp32 FMA GEMM on CUDA cores: A, B, B2 fp32.  The fp32 verification mode and the small
  * embedder GEMMs.  SWIGLU: N = hidden width, out [M,N]. */
@@ -106,6 +125,16 @@ int fitb200_gemm_f32(const fitb200_gemm_args* a, fitb200_stream_t stream);
  * rows alternate 16 rows of fc1_g with the matching 16 rows of fc1_x (bias packed alike);
  * out is [M, Hp]. */
 int fitb200_gemm_bf16_tc(const fitb200_gemm_args* a, fitb200_stream_t stream);
+
+/* ---- inputs of the GEMM LayerNorm + modulate prologue (fitb200_gemm_args.ln_*) -----------------------
+ * row_stats: parts[m, 0] = (sum_k x[m,k], sum_k x[m,k]^2), parts[m, 1..nparts) = 0 -- for a residual stream no GATE_RESID GEMM wrote
+ * (the embedder's output, fit.py:499-501).  x: [M, D] act dtype; parts: fp32 [M, nparts, 2].
+ * modulation_pack: out[set, s, :] = bf16(1 + scale_set[s, :]), out[set, S + s, :] = bf16(shift_set[s, :]) with
+ * shift_set = shift + set * set_stride, scale_set = scale + set * set_stride (fp32 rows of stride ld_mod: the adaLN chunks of fit.py:329-330;
+ * n_sets = 2 * blocks, set_stride = 3 D packs norm1 and norm2 of every block in one launch).  out: bf16 [n_sets, 2 S, D]. */
+int fitb200_row_stats(const void* x, int x_dtype, int M, int D, float* parts, int nparts, fitb200_stream_t stream);
+int fitb200_modulation_pack(const float* shift, const float* scale, int64_t ld_mod, int S, int D, int n_sets, int64_t set_stride, void* out,
+                            fitb200_stream_t stream);
 
 /* ---- LayerNorm(eps 1e-6, no affine) + adaLN modulate -------------------------------------------
  * modulate(norm(x), shift, scale) (fit.py:45-46,303,308,332,336): out = LN(x) * (1 + scale[s]) + shift[s],

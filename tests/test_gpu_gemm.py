@@ -180,3 +180,140 @@ def test_gemm_wgrad_ab_mn(ops, wdt, rows, N, K):
     out = torch.empty(N, K, dtype=torch.float32, device="cuda")
     ops.gemm(dY.cuda(), X.cuda(), None, out, EPI_BIAS, a_mn=True, b_mn=True)
     assert rel_l2(out, want) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------------- LayerNorm + modulate prologue (fit.py:45-46,332,336)
+def _ln_case(M, N, K, rps, seed, mean_shift=0.0):
+    g = torch.Generator().manual_seed(seed)
+    S = (M + rps - 1) // rps
+    x = (torch.randn(M, K, generator=g) * (0.5 + torch.rand(M, 1, generator=g)) + mean_shift * torch.randn(M, 1, generator=g)).bfloat16()
+    W = (torch.randn(N, K, generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, generator=g) * 0.1
+    mod = torch.randn(S, 3 * K, generator=g) * 0.3     # shift | scale | (gate: unused) -- strided views like the adaLN table
+    return x, W, bias, mod, S
+
+
+def _ln_reference(x, W, bias, mod, rps, K):
+    """modulate(LayerNorm(x), shift, scale) @ W^T + bias in fp64 on the same bf16 inputs."""
+    xd = x.double()
+    h = F.layer_norm(xd, (K,), eps=1e-6)
+    S = mod.shape[0]
+    sh = mod[:, :K].double().repeat_interleave(rps, 0)[:x.shape[0]]
+    sc = mod[:, K:2 * K].double().repeat_interleave(rps, 0)[:x.shape[0]]
+    return (h * (1 + sc) + sh) @ W.double().t() + bias.double()
+
+
+def _ln_operands(ops, x, W, bias, mod, S, K, N):
+    """What FiTEngine prepares: packed modulation rows, the (c1, c2) GEMM, the row sums."""
+    modc = mod.cuda()
+    packed = torch.empty(1, 2 * S, K, dtype=torch.bfloat16, device="cuda")
+    ops.modulation_pack(modc, modc[:, K:], 3 * K, S, K, 1, 3 * K, packed)
+    c = torch.empty(2 * S, N, dtype=torch.float32, device="cuda")
+    ops.gemm(packed[0], W.cuda(), bias.cuda(), c, EPI_BIAS, bias_row0=S)
+    parts = torch.full((x.shape[0], 3, 2), float("nan"), dtype=torch.float32, device="cuda")
+    ops.row_stats(x.cuda(), parts)
+    return packed[0, :S], c, parts
+
+
+LN_SHAPES = [(512, 3456, 1152, 256),      # the qkv shape: one sample per 256-row pair tile
+             (1024, 768, 768, 128),        # FiT-B width, one sample per CTA
+             (400, 432, 192, 256),         # ragged last row block and last sample, 3 k-slabs
+             (1000, 520, 1152, 128),       # cut last column tile, last row block partly beyond M
+             (38000, 256, 128, 384)]       # several tiles per CTA pair: ring / TMEM phases wrap under the A-producer warps
+
+
+@pytest.mark.parametrize("M,N,K,rps", LN_SHAPES)
+def test_gemm_ln_prologue_bias(ops, M, N, K, rps):
+    x, W, bias, mod, S = _ln_case(M, N, K, rps, M + N)
+    want = _ln_reference(x, W, bias, mod, rps, K)
+    g, c, parts = _ln_operands(ops, x, W, bias, mod, S, K, N)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(x.cuda(), W.cuda(), None, out, EPI_BIAS, rows_per_sample=rps, ln=(g, c, parts, 1e-6))
+    # the modulated operand is rounded to bf16 twice over (x * g, then the fp32 epilogue): same order as the stand-alone kernel's single rounding
+    assert rel_l2(out.float(), want) < 6e-3
+    # against the un-fused kernels on the same inputs: same result up to operand rounding
+    h = torch.empty(M, K, dtype=torch.bfloat16, device="cuda")
+    modc = mod.cuda()
+    ops.ln_modulate(x.cuda(), modc, modc[:, K:], 3 * K, rps, h)
+    ref = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(h, W.cuda(), bias.cuda(), ref, EPI_BIAS)
+    assert rel_l2(out.float(), ref.float()) < 8e-3
+
+
+def test_gemm_ln_prologue_row_mean(ops):
+    """Rows whose mean is several standard deviations: the mean is removed in the epilogue (mean * c1), not on the operand."""
+    M, N, K, rps = 512, 512, 1152, 256
+    x, W, bias, mod, S = _ln_case(M, N, K, rps, 3, mean_shift=3.0)
+    want = _ln_reference(x, W, bias, mod, rps, K)
+    g, c, parts = _ln_operands(ops, x, W, bias, mod, S, K, N)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(x.cuda(), W.cuda(), None, out, EPI_BIAS, rows_per_sample=rps, ln=(g, c, parts, 1e-6))
+    assert rel_l2(out.float(), want) < 2e-2
+
+
+@pytest.mark.parametrize("M,T,heads,hd", [(512, 256, 16, 72), (640, 128, 4, 64)])
+def test_gemm_ln_prologue_rope(ops, M, T, heads, hd):
+    D = heads * hd
+    N, K = 3 * D, D
+    x, W, bias, mod, S = _ln_case(M, N, K, T, M + T)
+    want = _ln_reference(x, W, bias, mod, T, K)
+    gen = torch.Generator().manual_seed(9)
+    ang = torch.rand(1, T, hd // 2, generator=gen) * 6.28
+    freqs = torch.stack([ang.cos(), ang.sin()], -1).reshape(1, T, hd).float().contiguous()
+    tok = torch.arange(M) % T
+    w2 = want[:, :2 * D].reshape(M, 2 * heads, hd // 2, 2)
+    cs = freqs[0, tok].double().reshape(M, 1, hd // 2, 2)
+    rot = torch.stack([w2[..., 0] * cs[..., 0] - w2[..., 1] * cs[..., 1], w2[..., 1] * cs[..., 0] + w2[..., 0] * cs[..., 1]], -1)
+    want = torch.cat([rot.reshape(M, 2 * D), want[:, 2 * D:]], 1)
+    g, c, parts = _ln_operands(ops, x, W, bias, mod, S, K, N)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(x.cuda(), W.cuda(), None, out, 4, rope=freqs.cuda(), rope_cols=2 * D, rows_per_sample=T, ln=(g, c, parts, 1e-6))
+    assert rel_l2(out.float(), want) < 6e-3
+
+
+@pytest.mark.parametrize("M,K,H,rps", [(512, 1152, 3072, 256), (300, 768, 2048, 128), (256, 1024, 2730, 256)])
+def test_gemm_ln_prologue_swiglu(ops, M, K, H, rps):
+    x, _, _, mod, S = _ln_case(M, 8, K, rps, M + H)
+    gen = torch.Generator().manual_seed(H)
+    Wg = (torch.randn(H, K, generator=gen) / K ** 0.5).bfloat16()
+    Wx = (torch.randn(H, K, generator=gen) / K ** 0.5).bfloat16()
+    bg, bx = torch.randn(H, generator=gen) * 0.1, torch.randn(H, generator=gen) * 0.1
+    want = F.silu(_ln_reference(x, Wg, bg, mod, rps, K)) * _ln_reference(x, Wx, bx, mod, rps, K)
+    Hp = (H + 15) // 16 * 16
+    wg, wx = torch.zeros(Hp, K, dtype=torch.bfloat16), torch.zeros(Hp, K, dtype=torch.bfloat16)
+    wg[:H], wx[:H] = Wg, Wx
+    b1, b2 = torch.zeros(Hp), torch.zeros(Hp)
+    b1[:H], b2[:H] = bg, bx
+    Wp = torch.stack([wg.view(Hp // 16, 16, K), wx.view(Hp // 16, 16, K)], 1).reshape(2 * Hp, K).contiguous()
+    bp = torch.stack([b1.view(Hp // 16, 16), b2.view(Hp // 16, 16)], 1).reshape(2 * Hp).contiguous()
+    g, c, parts = _ln_operands(ops, x, Wp, bp, mod, S, K, 2 * Hp)
+    out = torch.empty(M, Hp, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(x.cuda(), Wp.cuda(), None, out, EPI_SWIGLU, rows_per_sample=rps, ln=(g, c, parts, 1e-6))
+    assert rel_l2(out[:, :H].float(), want) < 8e-3
+    assert float(out[:, H:].float().abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("adt", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("M,N,K,rps", [(512, 1152, 1152, 256), (13200, 864, 192, 200), (300, 128, 64, 100)])
+def test_gemm_gate_residual_row_sums(ops, adt, M, N, K, rps):
+    """stats_out of the GATE_RESID epilogue: the partial sums add up to sum / sum of squares of every output row."""
+    A, B, bias = _inputs(M, N, K, M + N + 1, torch.bfloat16)
+    gen = torch.Generator().manual_seed(2)
+    R = (M + rps - 1) // rps
+    gate = torch.randn(R, N, generator=gen).cuda()
+    xs = torch.randn(M, N, generator=gen).to(adt).cuda()
+    parts = torch.full((M, ops.gemm_stats_parts(N), 2), float("nan"), dtype=torch.float32, device="cuda")
+    ops.gemm(A.cuda(), B.cuda(), bias.cuda(), xs, EPI_BIAS_GATE_RESID, gate=gate, ld_gate=N, rows_per_sample=rps, resid=xs, stats_out=parts)
+    s = parts.double().sum(1)
+    xd = xs.double()
+    tol = 2e-2 if adt == torch.bfloat16 else 1e-4   # the sums are of the fp32 values before the bf16 store
+    assert float((s[:, 0] - xd.sum(1)).abs().max()) < tol * float(xd.abs().sum(1).max())
+    assert rel_l2(s[:, 1].float(), (xd * xd).sum(1)) < tol
+
+
+def test_gemm_ln_prologue_argument_errors(ops):
+    x, W, bias, mod, S = _ln_case(400, 256, 128, 200, 1)
+    g, c, parts = _ln_operands(ops, x, W, bias, mod, S, 128, 256)
+    out = torch.empty(400, 256, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError, match="rows_per_sample"):   # CTA tiles would straddle samples: callers take the ln_modulate kernel
+        ops.gemm(x.cuda(), W.cuda(), None, out, EPI_BIAS, rows_per_sample=200, ln=(g, c, parts, 1e-6))

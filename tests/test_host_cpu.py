@@ -29,17 +29,24 @@ def test_header_cites_reference_lines():
     assert len(re.findall(r"(fit|gaussian_diffusion|dit|respace)\.py:\d+", src)) >= 15
 
 
-def test_gemm_args_struct_matches_header_layout():
-    from fit_b200._lib import GemmArgs
+def test_gemm_args_struct_matches_header_layout(tmp_path):
+    """Every field of the ctypes mirror sits at the offset the C compiler gives fitb200_gemm_args (gcc on include/fit_b200.h)."""
     import ctypes
-    # field order / offsets of fitb200_gemm_args on LP64
-    assert GemmArgs.M.offset == 0 and GemmArgs.K.offset == 8 and GemmArgs.A.offset == 16
-    assert GemmArgs.lda.offset == 24 and GemmArgs.B2.offset == 48 and GemmArgs.out.offset == 72
-    assert GemmArgs.out_dtype.offset == 88 and GemmArgs.epilogue.offset == 92 and GemmArgs.gate.offset == 96
-    assert GemmArgs.rows_per_sample.offset == 112 and GemmArgs.resid.offset == 120 and GemmArgs.resid_dtype.offset == 136
-    assert GemmArgs.rope_freqs.offset == 144 and GemmArgs.rope_rows.offset == 152 and GemmArgs.rope_cols.offset == 164
-    assert GemmArgs.a_mn.offset == 168 and GemmArgs.b_mn.offset == 172
-    assert ctypes.sizeof(GemmArgs) == 176
+    import subprocess
+    from fit_b200._lib import GemmArgs, HEADER_PATH
+    names = [f[0] for f in GemmArgs._fields_]
+    src = tmp_path / "off.c"
+    src.write_text('#include <stddef.h>\n#include <stdio.h>\n#include "%s"\nint main(void) {\n' % HEADER_PATH +
+                   "".join('  printf("%s %%zu\\n", offsetof(fitb200_gemm_args, %s));\n' % (n, n) for n in names) +
+                   '  printf("sizeof %zu\\n", sizeof(fitb200_gemm_args));\n  return 0;\n}\n')
+    exe = tmp_path / "off"
+    subprocess.run(["gcc", str(src), "-o", str(exe)], check=True)
+    lines = dict(l.split() for l in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for n in names:
+        assert getattr(GemmArgs, n).offset == int(lines[n]), n
+    assert ctypes.sizeof(GemmArgs) == int(lines["sizeof"])
+    # the round-1 fields keep their offsets (new fields are appended)
+    assert GemmArgs.M.offset == 0 and GemmArgs.A.offset == 16 and GemmArgs.rope_freqs.offset == 144 and GemmArgs.b_mn.offset == 172
 
 
 @pytest.mark.parametrize("rs", ["10", "250", "ddim25", ""])
