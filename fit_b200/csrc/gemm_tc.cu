@@ -22,17 +22,17 @@ namespace fitb200 {
 constexpr int GT_BM = 128, GT_BK = 64;
 constexpr int GT_THREADS = 320;  // producer + mma + 8 epilogue warps
 constexpr int GT_EPI_THREADS = 256;  // two warps per TMEM lane quarter: each takes half of a slab's columns
-// LNA kernels (LayerNorm + adaLN modulate prologue): 20 warps in five warpgroups, so that setmaxnreg can move registers between the roles --
-//   warps 0..3   TMA producer (B), MMA issuer, relay thread (publishes the A rows to the tensor core), one idle warp      32 registers
-//   warps 4..11  epilogue                                                                                                  144 registers
-//   warps 12..19 A producers: two warps per scheduler (one warp each was issue-latency bound: 805 clk per k-slab),         96 registers
-//                three k-slabs of 4 rows x 16 bytes in flight per thread
-constexpr int GT_LNA_THREADS = 256;
-constexpr int GT_THREADS_LNA = 640;
-constexpr int GT_LNA_ROWS = 128 / (GT_LNA_THREADS / 8);   // rows per producer thread
+// LNA kernels (LayerNorm + adaLN modulate prologue): 16 warps in four warpgroups, so that setmaxnreg can move registers between the roles --
+//   warps 0..3   TMA producer (raw x rows + B), MMA issuer, relay thread (publishes the rescaled A rows to the tensor core), one idle warp
+//   warps 4..11  epilogue
+//   warps 12..15 A rescalers: x * bf16(1 + scale) in place in the shared-memory ring slot TMA filled
+constexpr int GT_LNA_THREADS = 128;
+constexpr int GT_THREADS_LNA = 512;
+constexpr int GT_LNA_ROWS = 128 / (GT_LNA_THREADS / 8);   // rows per rescaler thread
+constexpr int GT_BAR_BYTES = 512;
 constexpr int GT_SLAB_BYTES = GT_BM * 128;  // 128 rows x 128 bytes
 constexpr int GT_ROPE_MAX_HD = 72;          // head dims up to this keep the tile's RoPE rows in shared memory (FiT: 64, 72)
-constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - 256 /*barriers*/;
+constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - GT_BAR_BYTES /*barriers*/;
 
 // PAIR: two CTAs of a cluster (one TPC) share one 256 x BN tile through tcgen05 cta_group::2 -- each CTA stages its own 128 rows of A
 // and HALF of the B rows, so the shared-memory bytes read per MMA flop drop by a third (a 128 x 192 single-CTA tile needs 106 of the
@@ -50,7 +50,7 @@ template <int BN, int EPI, bool PAIR = false, bool LNA = false> struct GtCfg {
   static constexpr int STAGES_RAW = (GT_SMEM_BUDGET - EPI_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > (PAIR ? 8 : 6) ? (PAIR ? 8 : 6) : STAGES_RAW;
   static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;  // 2 accumulator stages, power of two
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + GT_BAR_BYTES;
   static_assert(STAGES >= 3, "pipeline too shallow");
   static_assert(!PAIR || (BNL % 8 == 0 && BN % 16 == 0), "pair tile: N a multiple of 16");
 };
@@ -87,9 +87,10 @@ __device__ __forceinline__ void tmem_ld16f(uint32_t taddr, float* v) {
 // LNA: the A operand is modulate(LayerNorm(x), shift, scale) (fit.py:45-46,303,308,332,336) of the raw residual stream x, formed inside this kernel
 // instead of by a separate pass over HBM.  With g = 1 + scale[s], mu / rstd the row statistics:
 //     sum_k ((x - mu) rstd g_k + shift_k) W[n,k]  =  rstd (sum_k (x g_k) W[n,k]  -  mu c1[s,n])  +  c2[s,n]
-// so the only per-element work on the operand path is ONE packed bf16 multiply x * bf16(g_k): four extra warps load x from global memory
-// (16-byte loads, two k-slabs ahead), multiply, and store into the 128B-swizzled A ring the MMA reads (no extra shared-memory traffic:
-// the store replaces TMA's); mu, rstd, c1, c2 are applied to the fp32 accumulators in the epilogue.  c1 / c2 are [samples, N] vectors
+// so the only per-element work on the operand path is ONE packed bf16 multiply x * bf16(g_k): TMA delivers the raw x rows into the A ring as
+// for any GEMM, four extra warps rescale them in place (ld.shared / HMUL2 / st.shared on the 128B-swizzled slot) before the MMA reads them;
+// mu, rstd, c1, c2 are applied to the fp32 accumulators in the epilogue.  (First version: the warps loaded x themselves with 16-byte global
+// loads -- the same bytes through the LSU / L1 instead of TMA: 65 % tensor pipe against 80 %, profiles/r2b_ln_prologue.txt.)  c1 / c2 are [samples, N] vectors
 // from a small GEMM of the modulation rows with the same weight; the row sums come from the GATE_RESID epilogue that wrote x.
 template <int BN, int EPI, typename OutT, bool AMN = false, bool BMN = false, bool PAIR = false, bool LNA = false>
 __global__ void __launch_bounds__(LNA ? GT_THREADS_LNA : GT_THREADS, 1)
@@ -129,8 +130,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       epilogue -> MMA
   uint64_t* res_bar = bars + 2 * STAGES + 4;     // [4][2]    residual slab rows of lane quarter q landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
-  uint64_t* abar = bars + 2 * STAGES + 13;       // [STAGES]  LNA: A-producer warps -> relay thread
-  static_assert(!LNA || 3 * STAGES + 13 <= 32, "barrier area is 256 bytes");
+  uint64_t* abar = bars + 2 * STAGES + 13;       // [STAGES]  LNA: rescaler warps -> relay thread
+  uint64_t* rbar = bars + 3 * STAGES + 13;       // [STAGES]  LNA: TMA (raw x rows of THIS CTA landed) -> rescaler warps
+  static_assert(4 * STAGES + 13 <= GT_BAR_BYTES / 8, "barrier area");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_n = ceil_div(p.N, BN), tiles_m = ceil_div(p.M, TM);
@@ -151,7 +153,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int s = 0; s < STAGES; ++s) {
       ptx::mbar_init(&full_bar[s], LNA ? 1 + (PAIR ? 2 : 1) : 1);
       ptx::mbar_init(&empty_bar[s], 1);
-      if (LNA) ptx::mbar_init(&abar[s], LNA_WARPS);
+      if (LNA) { ptx::mbar_init(&abar[s], LNA_WARPS); ptx::mbar_init(&rbar[s], 1); }
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
@@ -171,7 +173,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t tmem_base = *tmem_slot;
   // LNA: registers follow the work -- every warp of a warpgroup executes the same setmaxnreg, first thing in its role branch
   if (warp == 0) {
-    if (LNA) ptx::setmaxnreg_dec<32>();
+    if (LNA) ptx::setmaxnreg_dec<40>();
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
@@ -189,7 +191,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * stage_bytes);
             const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
             if (LNA) {
-              // A is written by the A-producer warps
+              // raw x rows of this CTA -> its own ring slot, announced to its own rescaler warps (not to the MMA's full barrier)
+              ptx::mbar_arrive_expect_tx(&rbar[stage], Cfg::A_BYTES);
+              ptx::tma_load_2d(smemA + stage * Cfg::A_BYTES, &tmA, &rbar[stage], kb * GT_BK, m0);
             } else if (AMN) {
 #pragma unroll
               for (int b = 0; b < GT_BM / 64; ++b) ptx::tma_load_2d_pair(smemA + stage * Cfg::A_BYTES + b * 8192, &tmA, fb, m0 + b * 64, kb * GT_BK);
@@ -225,7 +229,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (LNA) ptx::setmaxnreg_dec<32>();
+    if (LNA) ptx::setmaxnreg_dec<40>();
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0 && rank == 0) {
       constexpr uint32_t idesc0 = ptx::idesc_bf16_f32(TM, 0) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
@@ -267,7 +271,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else if (LNA && warp == 2) {
-    ptx::setmaxnreg_dec<32>();
+    ptx::setmaxnreg_dec<40>();
     // ------------------------------------------------------------------ relay thread (LNA): A rows stored -> proxy fence -> MMA's full barrier
     if (lane == 0) {
       const uint32_t full_leader = PAIR ? ptx::mapa(ptx::smem_u32(&full_bar[0]), 0) : ptx::smem_u32(&full_bar[0]);
@@ -283,90 +287,77 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else if (LNA && warp == 3) {
-    ptx::setmaxnreg_dec<32>();  // idle: fills the first warpgroup
+    ptx::setmaxnreg_dec<40>();  // idle: fills the first warpgroup
   } else if (LNA && warp >= EPI_WARP0 + GT_EPI_THREADS / 32) {
     // ------------------------------------------------------------------ A-producer warps (LNA): x * bf16(1 + scale) -> swizzled A ring
     // thread = (16-byte chunk c of the 128-byte k-slab row, row group rg): rows rg, rg + 16, ... rg + 112 of this CTA's 128 rows.  One warp
     // instruction reads 4 rows x 128 contiguous bytes and stores 512 contiguous (chunk-permuted) bytes: coalesced and conflict-free.
-    ptx::setmaxnreg_dec<96>();   // (no change: the launch allocates 96 per thread)
+    ptx::setmaxnreg_dec<72>();
     constexpr int NR = GT_LNA_ROWS, RSTEP = GT_LNA_THREADS / 8;   // rows per thread, row distance between them
     const int pt = (int)threadIdx.x - (EPI_WARP0 * 32 + GT_EPI_THREADS);
     const int c = pt & 7, rg = pt >> 3;
-    // (rg + 32 j) & 7 == rg & 7: the swizzle phase is per thread.  All shared-memory addresses are 32-bit shared-window addresses so that the
-    // loop below issues few instructions per k-slab (the first version spent ~300 on 64-bit address arithmetic and was issue-bound)
+    // thread = (16-byte chunk c of the 128-byte k-slab row, row group rg): rows rg, rg + 16, ... of this CTA's 128 rows; (rg + 16 j) & 7 ==
+    // rg & 7, so the 128B-swizzle phase is per thread.  One warp instruction touches 4 rows x 128 contiguous (chunk-permuted) bytes:
+    // conflict-free.  32-bit shared-window addresses throughout.
     const uint32_t dst0 = ptx::smem_u32(smemA) + (uint32_t)(rg * 128 + ((c ^ (rg & 7)) << 4));
-    const uint32_t empty0 = ptx::smem_u32(&empty_bar[0]), abar0 = ptx::smem_u32(&abar[0]);
+    const uint32_t rbar0 = ptx::smem_u32(&rbar[0]), abar0 = ptx::smem_u32(&abar[0]);
     const int my_tiles = wid < num_tiles ? (num_tiles - 1 - wid) / nwork + 1 : 0;
     const int total = my_tiles * num_kb;
-    // fetch cursor (three k-slabs ahead of the store cursor) and its per-tile state: byte pointer to (first row of this thread, its chunk),
-    // byte offsets of its rows from there (rows beyond M repeat the last existing one: their output rows are clipped by the store), the
-    // modulation row.  rows_per_sample % 128 == 0 (checked on the host): the 128 rows of a CTA tile belong to one sample, so one 16-byte load
-    // of bf16(1 + scale) per thread and k-slab serves all its rows; each chunk is read once per CTA and tile (an L2 hit, never an L1 hit), so
-    // it is prefetched with the rows.
+    // bf16(1 + scale) of the slab's 8 columns of this thread.  rows_per_sample % 128 == 0 (checked on the host): the 128 rows of a CTA tile
+    // belong to one sample, so one 16-byte load per thread and k-slab serves all its rows; each chunk is read once per CTA and tile (an L2
+    // hit, never an L1 hit), so it is fetched three k-slabs ahead.  K % 64 == 0 (checked on the host): every k-slab is whole.
     int f_it = 0, f_kb = 0;
-    const char* xbase = nullptr;
     const char* gbase = nullptr;
-    uint32_t roff[NR];
-    const uint32_t rstride = (uint32_t)(RSTEP * p.ld_lnx * 2);
     auto enter_tile = [&]() {
       const int m0 = ((wid + f_it * nwork) / tiles_n) * TM + row_off;
-      const int r0 = min(m0 + rg, p.M - 1);
-      xbase = reinterpret_cast<const char*>(p.lnx + (size_t)r0 * p.ld_lnx + c * 8);
-      const int jmax = min(NR - 1, (p.M - 1 - r0) / RSTEP);
-#pragma unroll
-      for (int j = 0; j < NR; ++j) roff[j] = (uint32_t)min(j, jmax) * rstride;
       gbase = reinterpret_cast<const char*>(p.lng + (size_t)(min(m0, p.M - 1) / p.rows_per_sample) * p.ld_lng + c * 8);
     };
     if (total > 0) enter_tile();
-    auto fetch = [&](uint4 (&b)[NR], uint4& g) {   // K % 64 == 0 (checked on the host): every k-slab is whole
-      const uint32_t kb2 = (uint32_t)f_kb * (GT_BK * 2);
-      const char* xk = xbase + kb2;
-#pragma unroll
-      for (int j = 0; j < NR; ++j) b[j] = __ldg(reinterpret_cast<const uint4*>(xk + roff[j]));
-      g = __ldg(reinterpret_cast<const uint4*>(gbase + kb2));
+    auto fetch = [&](uint4& g) {
+      g = __ldg(reinterpret_cast<const uint4*>(gbase + (uint32_t)f_kb * (GT_BK * 2)));
       if (++f_kb == num_kb) { f_kb = 0; ++f_it; if (f_it < my_tiles) enter_tile(); }
     };
     int stage = 0; uint32_t phase = 0;
-    auto store = [&](uint4 (&b)[NR], const uint4& g) {
-      ptx::mbar_wait_addr(empty0 + stage * 8, phase ^ 1);   // the MMAs that read this slot (of both CTAs) have retired
+    auto rescale = [&](const uint4& g) {
+      ptx::mbar_wait_addr(rbar0 + stage * 8, phase);   // TMA has written this CTA's raw rows of the slot
       const uint32_t dst = dst0 + stage * Cfg::A_BYTES;
       const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&g);
+      uint4 v[NR];
+#pragma unroll
+      for (int j = 0; j < NR; ++j) v[j] = ptx::ld_shared_v4(dst + j * RSTEP * 128);
 #pragma unroll
       for (int j = 0; j < NR; ++j) {
-        uint4 v = b[j];
-        __nv_bfloat162* v2 = reinterpret_cast<__nv_bfloat162*>(&v);
+        __nv_bfloat162* v2 = reinterpret_cast<__nv_bfloat162*>(&v[j]);
 #pragma unroll
         for (int e = 0; e < 4; ++e) v2[e] = __hmul2(v2[e], g2[e]);
-        ptx::st_shared_v4(dst + j * RSTEP * 128, v);
+        ptx::st_shared_v4(dst + j * RSTEP * 128, v[j]);
       }
-      // hand the rows to the relay thread with a plain CTA-scope arrive.  The generic -> async proxy fence the tensor core's operand reads need
-      // is NOT executed here: it compiles to MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC, and a MEMBAR waits for every load the thread has in flight
-      // -- the prefetched k-slabs.  The relay thread has no loads in flight.
+      // hand the rows to the relay thread (CTA-scope arrive); it executes the generic -> async proxy fence the tensor core's operand reads
+      // need and arrives on the MMA's full barrier
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_addr(abar0 + stage * 8);
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     };
-    // three register buffers: the loads of a k-slab are in flight for three slab periods (~1500 clk) before their values are needed
     const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-    uint4 b0[NR], b1[NR], b2[NR], g0 = z4, g1 = z4, g2 = z4;
-    if (total > 0) fetch(b0, g0);
-    if (total > 1) fetch(b1, g1);
-    if (total > 2) fetch(b2, g2);
+    uint4 g0 = z4, g1 = z4, g2 = z4;
+    if (total > 0) fetch(g0);
+    if (total > 1) fetch(g1);
+    if (total > 2) fetch(g2);
     for (int i = 0; i < total; i += 3) {
-      store(b0, g0);
-      if (i + 3 < total) fetch(b0, g0);
+      rescale(g0);
+      if (i + 3 < total) fetch(g0);
       if (i + 1 < total) {
-        store(b1, g1);
-        if (i + 4 < total) fetch(b1, g1);
+        rescale(g1);
+        if (i + 4 < total) fetch(g1);
       }
       if (i + 2 < total) {
-        store(b2, g2);
-        if (i + 5 < total) fetch(b2, g2);
+        rescale(g2);
+        if (i + 5 < total) fetch(g2);
       }
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps (2..9)
-    if (LNA) ptx::setmaxnreg_inc<128>();
+    if (LNA) ptx::setmaxnreg_inc<168>();
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
     const int half = (warp - EPI_WARP0) >> 2;  // which half of each slab's columns this warp handles
     const int row = quarter * 32 + lane;     // row inside the tile == TMEM lane

@@ -98,11 +98,13 @@ LN_EPS = 1e-6  # norm1 / norm2 (fit.py:303,308)
 
 
 def ln_prologue_ok(precision: str, M: int, D: int, T: int) -> bool:
-    """The GEMM LayerNorm + modulate prologue (gemm_tc.cu, LNA) serves the bf16 path when every 128-row CTA tile lies inside one sample
-    (T % 128 == 0: the reference's 256-token sequences and the 1024 / 4096-token extrapolation shapes) and the width is a whole number of
-    64-column k-slabs (every FiT size: 384, 768, 1024, 1152); FITB200_LN_FUSE=0 keeps the stand-alone
-    ln_modulate kernel (A/B measurements, and the path every other shape takes)."""
-    return precision == "bf16" and M > 128 and T % 128 == 0 and D > 128 and D % 64 == 0 and os.environ.get("FITB200_LN_FUSE", "1") != "0"
+    """Whether FiTEngine runs modulate(norm(x)) as the PROLOGUE of the qkv / fc1 GEMMs (gemm_tc.cu, LNA) instead of the stand-alone
+    ln_modulate kernel.  Opt-in (FITB200_LN_FUSE=1): parity-green, but measured SLOWER on the headline step (128.6 vs 122.6 ms,
+    profiles/r2b_ln_prologue.txt) -- the 256 x 256 pair-tile mainloop already sits at the shared-memory / L2->SM bandwidth edge, and rescaling
+    the operand on its way to the tensor core costs it more (65-70 % tensor pipe instead of 80 %) than the separate 0.13 ms pass over HBM.
+    Shapes served: bf16, every 128-row CTA tile inside one sample (T % 128 == 0: the reference's 256-token sequences and the 1024 / 4096-token
+    extrapolation shapes), width a whole number of 64-column k-slabs (every FiT size: 384, 768, 1024, 1152)."""
+    return precision == "bf16" and M > 128 and T % 128 == 0 and D > 128 and D % 64 == 0 and os.environ.get("FITB200_LN_FUSE", "0") == "1"
 
 
 class _Workspace:

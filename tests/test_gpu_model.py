@@ -77,6 +77,35 @@ def test_real_width_forward_matches_reference(name, model_name, shapes, precisio
     assert rel_l2(oc, z["out_cfg"]) < tol
 
 
+@pytest.mark.parametrize("name,model_name,shapes", [("fit_b2_mixed", "FiT-B/2", [(32, 32), (20, 40), (16, 64)]),
+                                                    ("fit_xl2_small", "FiT-XL/2", [(32, 32), (20, 40)])])
+def test_ln_prologue_forward_matches_reference(monkeypatch, name, model_name, shapes):
+    """The opt-in path (FITB200_LN_FUSE=1): modulate(norm1/norm2(x)) (fit.py:332,336) formed inside the qkv / fc1 GEMMs -- row sums from the
+    proj / fc2 epilogues, operand rescaled in shared memory, mean / rstd / shift applied to the accumulators -- against the reference's goldens,
+    and against the default (stand-alone ln_modulate) path on the same weights."""
+    monkeypatch.setenv("FITB200_LN_FUSE", "1")
+    z = golden(name)
+    cfg = fo.model_config(model_name)
+    sd = fo.random_state_dict(cfg, seed=7)
+    d = cfg["hidden_size"] // cfg["num_heads"]
+    x, t, y, pos, mask, target = synth.mixed_batch(cfg, shapes, 256, seed=11, rope_dim=d)
+    model = build_model(cfg, sd, "bf16")
+    with torch.no_grad():
+        out = model(x.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda(), train=True)
+    ws = model.engine.workspace(x.shape[0], 256, torch.device("cuda", torch.cuda.current_device()))
+    assert ws.modA is not None, "the fused path was not taken"
+    err = _valid_rel(out, z["out_train"], mask)
+    monkeypatch.setenv("FITB200_LN_FUSE", "0")
+    plain = build_model(cfg, sd, "bf16")
+    with torch.no_grad():
+        out0 = plain(x.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda(), train=True)
+    assert plain.engine.workspace(x.shape[0], 256, torch.device("cuda", torch.cuda.current_device())).modA is None
+    err0 = _valid_rel(out0, z["out_train"], mask)
+    from helpers import record
+    record(f"ln_prologue forward {model_name} [bf16] rel-L2 fused / un-fused", f"{err:.3e} / {err0:.3e}")
+    assert err < 2e-2 and err < 2.0 * err0 + 1e-3
+
+
 def test_padded_tokens_never_influence_valid_tokens():
     """Size-independent property: garbage in the padded token slots changes no valid output bit."""
     cfg = fo.model_config("FiT-B/2", depth=2)
