@@ -362,7 +362,7 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
     import torch.distributed as dist
     from fit_b200 import _lib as L
     from fit_b200.optim import FusedAdamWEMA
-    from fit_b200.train import GradSync, masked_mse_loss
+    from fit_b200.train import GradSync, attach_optimizer, masked_mse_loss
     from fit_b200.rope import precompute_freqs_cis_2d
     D, Hd, Ld, heads = MODELS[args.model]
     T, d = 256, D // heads
@@ -376,7 +376,7 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
     pos = torch.tensor(precompute_freqs_cis_2d(d, 16, 16, max_length=256), dtype=torch.float32)[None].expand(samples, T, d).contiguous().to(dev)
     mask = torch.ones(samples, T, dtype=torch.bool, device=dev)
     sync = GradSync().attach(model) if world > 1 else None
-    opt = FusedAdamWEMA(model.parameters(), lr=1e-4, weight_decay=0.0, ema_decay=0.9999)
+    opt = attach_optimizer(model, FusedAdamWEMA(model.parameters(), lr=1e-4, weight_decay=0.0, ema_decay=0.9999))
 
     def step(do_opt=True):
         for p in model.parameters():

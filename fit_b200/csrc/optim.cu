@@ -1,7 +1,8 @@
 // Training-loop neighbours of the hot path.
 // (1) Fused multi-tensor AdamW + EMA step (row f3).  Replaces torch.optim.AdamW.step (FiT/train.py:215-217) and the EMA
 // wrapper's _foreach_mul_ / _foreach_add_ pair on a side stream (FiT/ema.py:149-154,256-267) by ONE pass: every element of
-// (p, g, m, v, ema) is read once and (p, m, v, ema) written once -- 36 B per element, HBM-bound (FiT-XL/2: 674.9 M elements = 24.3 GB).
+// (p, g, m, v, ema) is read once and (p, m, v, ema) written once -- 36 B per element, HBM-bound (FiT-XL/2: 674.9 M elements = 24.3 GB);
+// optionally the bf16 / packed copy of the parameter that the GEMMs read is written in the same pass (+2 B per element).
 // One CTA = one FITB200_ADAM_CHUNK-element chunk of one tensor (chunk table built once by the host), 16-byte accesses, grid = chunks.
 #include "common.cuh"
 
@@ -23,6 +24,12 @@ __global__ void __launch_bounds__(256) adamw_ema_kernel(const fitb200_adam_tenso
   const float step = sc.step, decay_p = sc.decay_p, omb1 = sc.omb1, beta2 = sc.beta2, omb2 = sc.omb2, bc2_sqrt = sc.bc2_sqrt, eps = sc.eps,
               ema_decay = sc.ema_decay, ome = sc.ome;
   const bool do_ema = e != nullptr && ema_decay >= 0.f;
+  // kernel-layout copy of the updated parameter (fitb200_adam_tensor.shadow)
+  auto shadow_index = [&](int64_t idx) {
+    const int64_t row = idx / t.row_len, col = idx - row * t.row_len;
+    const int64_t srow = t.pack_off < 0 ? row : (row >> 4) * 32 + t.pack_off + (row & 15);
+    return srow * t.shadow_ld + col;
+  };
   auto upd = [&](float& pp, float gg, float& mm, float& vv, float& ee) {
     pp *= decay_p;
     mm = mm + (gg - mm) * omb1;                       // exp_avg.lerp_(grad, 1 - beta1)
@@ -43,12 +50,37 @@ __global__ void __launch_bounds__(256) adamw_ema_kernel(const fitb200_adam_tenso
     reinterpret_cast<float4*>(m)[i] = m4;
     reinterpret_cast<float4*>(v)[i] = v4;
     if (do_ema) reinterpret_cast<float4*>(e)[i] = e4;
+    if (t.shadow) {
+      const int64_t idx = base + 4 * (int64_t)i;
+      if ((t.row_len & 3) == 0 && (t.shadow_ld & 3) == 0) {   // the four elements share a row: one 8- or 16-byte store
+        const int64_t si = shadow_index(idx);
+        if (t.shadow_dtype == FITB200_BF16) {
+          uint2 o; o.x = pack_bf16x2(p4.x, p4.y); o.y = pack_bf16x2(p4.z, p4.w);
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(t.shadow) + si) = o;
+        } else {
+          *reinterpret_cast<float4*>(reinterpret_cast<float*>(t.shadow) + si) = p4;
+        }
+      } else {
+        const float pv[4] = {p4.x, p4.y, p4.z, p4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int64_t si = shadow_index(idx + k);
+          if (t.shadow_dtype == FITB200_BF16) reinterpret_cast<__nv_bfloat16*>(t.shadow)[si] = __float2bfloat16_rn(pv[k]);
+          else reinterpret_cast<float*>(t.shadow)[si] = pv[k];
+        }
+      }
+    }
   }
   for (int i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) {
     float pp = p[i], mm = m[i], vv = v[i], ee = do_ema ? e[i] : 0.f;
     upd(pp, g[i], mm, vv, ee);
     p[i] = pp; m[i] = mm; v[i] = vv;
     if (do_ema) e[i] = ee;
+    if (t.shadow) {
+      const int64_t si = shadow_index(base + i);
+      if (t.shadow_dtype == FITB200_BF16) reinterpret_cast<__nv_bfloat16*>(t.shadow)[si] = __float2bfloat16_rn(pp);
+      else reinterpret_cast<float*>(t.shadow)[si] = pp;
+    }
   }
 }
 

@@ -21,6 +21,7 @@ import torch
 
 from . import ops
 from ._lib import EPI_BIAS, EPI_BIAS_GATE_RESID, EPI_BIAS_ROPE, EPI_BIAS_SILU, EPI_SWIGLU
+from ._nvtx import rng
 
 Tensor = torch.Tensor
 
@@ -365,20 +366,23 @@ class FiTEngine:
         ws = self.workspace(R, T, x.device)
         t = t.to(torch.int64) if t.dtype != torch.int64 else t
         y = y.to(torch.int64) if y.dtype != torch.int64 else y
-        ops.mask_to_kvlen(mask, ws.kv_len, ws.n_valid)
-        ops.embed_tokens(x, W.x_w, W.x_b, ws.xs, R, T, p, C_in)
-        self.conditioning(ws, W, t, y)
-        if ws.modA is not None:
-            ops.row_stats(ws.xs, ws.parts)
+        with rng("fit/embed+conditioning"):
+            ops.mask_to_kvlen(mask, ws.kv_len, ws.n_valid)
+            ops.embed_tokens(x, W.x_w, W.x_b, ws.xs, R, T, p, C_in)
+            self.conditioning(ws, W, t, y)
+            if ws.modA is not None:
+                ops.row_stats(ws.xs, ws.parts)
         if collect is not None:
             collect.append(ws.xs.float().view(R, T, D).clone())
         for i in range(len(m.blocks)):
-            self.block(i, ws, W, pos, mask)
+            with rng(f"fit/block/{i}"):
+                self.block(i, ws, W, pos, mask)
             if collect is not None:
                 collect.append(ws.xs.float().view(R, T, D).clone())
         P = p * p * m.out_channels
         if out is None:
             out = torch.empty((R, T, P) if train else (R, m.out_channels, H, Wd), dtype=torch.float32, device=x.device)
         sh, sc = ws.fin_views
-        ops.final_layer(ws.xs, sh, sc, W.n_mod, W.fin_w, W.fin_b, out, R, T, p, m.out_channels)
+        with rng("fit/final_layer"):
+            ops.final_layer(ws.xs, sh, sc, W.n_mod, W.fin_w, W.fin_b, out, R, T, p, m.out_channels)
         return out

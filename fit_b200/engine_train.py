@@ -18,6 +18,7 @@ import torch
 
 from . import ops
 from ._lib import EPI_BIAS, EPI_BIAS_ROPE
+from ._nvtx import rng
 
 Tensor = torch.Tensor
 
@@ -27,55 +28,94 @@ def _round_up(a: int, b: int) -> int:
 
 
 class TrainWeights:
-    """Parameters in kernel layout for the training path (act dtype; fc1_g | fc1_x packed in groups of 16 rows)."""
+    """Parameters in kernel layout for the training path (act dtype; fc1_g | fc1_x packed in groups of 16 rows).
+
+    The buffers are allocated ONCE and refilled in place (``refresh``), so their addresses can be handed to the optimizer:
+    ``FusedAdamWEMA.attach_engine`` makes the fused AdamW kernel write the bf16 / packed copy of every updated parameter straight into
+    them (``shadow_specs``), and nothing re-casts or re-packs the 675 M parameters after a step.  fp32 tensors the kernels read in the
+    parameter's own layout (biases of qkv / proj / fc2, the embedders) are views of the parameters themselves."""
 
     def __init__(self, model, precision: str):
         D, L = model.hidden_size, len(model.blocks)
         self.H = H = model.blocks[0].ffn.hidden_features
         self.Hp = Hp = _round_up(H, 16)
+        self.D = D
         wdt = torch.bfloat16 if precision == "bf16" else torch.float32
         self.wdt = wdt
+        dev = model.y_embedder.embedding_table.weight.device
+        self.t_freqs = torch.exp(-math.log(10000.0) * torch.arange(128, dtype=torch.float32) / 128).to(dev)  # fit.py:73-75
+        self.n_mod = 6 * D * L + 2 * D
+        self.ada_w = torch.empty(self.n_mod, D, device=dev, dtype=wdt)
+        self.ada_b = torch.empty(self.n_mod, device=dev, dtype=torch.float32)
+        self.blocks = []
+        for _ in model.blocks:
+            e = {"qkv_w": torch.empty(3 * D, D, device=dev, dtype=wdt), "proj_w": torch.empty(D, D, device=dev, dtype=wdt),
+                 "fc1_w": torch.zeros(2 * Hp, D, device=dev, dtype=wdt), "fc1_b": torch.zeros(2 * Hp, device=dev, dtype=torch.float32),
+                 "fc2_w": torch.zeros(D, Hp, device=dev, dtype=wdt)}   # padded rows / columns (FiT-L) stay zero
+            self.blocks.append(e)
+        self.fin_w = torch.empty(model.final_layer.linear.weight.shape, device=dev, dtype=wdt)
+        self.refresh(model)
+
+    def refresh(self, model):
+        """(Re)fill every buffer from the fp32 parameters: after construction, load_state_dict, an EMA swap -- any parameter change that did
+        not come from the attached optimizer."""
+        D, H, Hp = self.D, self.H, self.Hp
 
         def f32(p):
-            return p.detach().float().contiguous()
-
-        def w(p):
-            return p.detach().to(wdt).contiguous()
+            return p.detach().float().contiguous()   # fp32 contiguous parameters: a view, not a copy
 
         self.x_w, self.x_b = f32(model.x_embedder.weight), f32(model.x_embedder.bias)
         self.t0_w, self.t0_b = f32(model.t_embedder.mlp[0].weight), f32(model.t_embedder.mlp[0].bias)
         self.t2_w, self.t2_b = f32(model.t_embedder.mlp[2].weight), f32(model.t_embedder.mlp[2].bias)
         self.y_table = f32(model.y_embedder.embedding_table.weight)
-        dev = self.y_table.device
-        self.t_freqs = torch.exp(-math.log(10000.0) * torch.arange(128, dtype=torch.float32) / 128).to(dev)  # fit.py:73-75
-        ada_w = [b.adaLN_modulation[1].weight for b in model.blocks] + [model.final_layer.adaLN_modulation[1].weight]
-        ada_b = [b.adaLN_modulation[1].bias for b in model.blocks] + [model.final_layer.adaLN_modulation[1].bias]
-        self.ada_w = torch.cat([p.detach() for p in ada_w], 0).to(wdt).contiguous()
-        self.ada_b = torch.cat([p.detach() for p in ada_b], 0).float().contiguous()
-        self.n_mod = self.ada_w.shape[0]
-        self.blocks = []
-        for blk in model.blocks:
-            e = {"qkv_w": w(blk.attn.qkv.weight), "qkv_b": f32(blk.attn.qkv.bias),
-                 "proj_w": w(blk.attn.proj.weight), "proj_b": f32(blk.attn.proj.bias)}
-            fg, fx = blk.ffn.fc1_g, blk.ffn.fc1_x
-            wg = torch.zeros(Hp, D, device=dev, dtype=wdt)
-            wx = torch.zeros(Hp, D, device=dev, dtype=wdt)
-            wg[:H], wx[:H] = fg.weight.detach().to(wdt), fx.weight.detach().to(wdt)
-            bg = torch.zeros(Hp, device=dev)
-            bx = torch.zeros(Hp, device=dev)
-            bg[:H], bx[:H] = fg.bias.detach().float(), fx.bias.detach().float()
-            e["fc1_w"] = torch.stack([wg.view(Hp // 16, 16, D), wx.view(Hp // 16, 16, D)], 1).reshape(2 * Hp, D).contiguous()
-            e["fc1_b"] = torch.stack([bg.view(Hp // 16, 16), bx.view(Hp // 16, 16)], 1).reshape(2 * Hp).contiguous()
-            w2 = blk.ffn.fc2.weight.detach()
-            if Hp != H:
-                w2p = torch.zeros(D, Hp, device=dev, dtype=wdt)
-                w2p[:, :H] = w2.to(wdt)
-                e["fc2_w"] = w2p
-            else:
-                e["fc2_w"] = w2.to(wdt).contiguous()
-            e["fc2_b"] = f32(blk.ffn.fc2.bias)
-            self.blocks.append(e)
-        self.fin_w, self.fin_b = w(model.final_layer.linear.weight), f32(model.final_layer.linear.bias)
+        for i, lin in enumerate(self._ada_linears(model)):
+            o, n = self._ada_slice(i)
+            self.ada_w[o:o + n].copy_(lin.weight.detach())
+            self.ada_b[o:o + n].copy_(lin.bias.detach())
+        for blk, e in zip(model.blocks, self.blocks):
+            e["qkv_w"].copy_(blk.attn.qkv.weight.detach())
+            e["proj_w"].copy_(blk.attn.proj.weight.detach())
+            e["qkv_b"], e["proj_b"], e["fc2_b"] = f32(blk.attn.qkv.bias), f32(blk.attn.proj.bias), f32(blk.ffn.fc2.bias)
+            w1 = e["fc1_w"].view(Hp // 16, 2, 16, D)
+            b1 = e["fc1_b"].view(Hp // 16, 2, 16)
+            for half, lin in enumerate((blk.ffn.fc1_g, blk.ffn.fc1_x)):
+                full, rem = H // 16, H % 16
+                w1[:full, half].copy_(lin.weight.detach()[:full * 16].view(full, 16, D))
+                b1[:full, half].copy_(lin.bias.detach()[:full * 16].view(full, 16))
+                if rem:
+                    w1[full, half, :rem].copy_(lin.weight.detach()[full * 16:])
+                    b1[full, half, :rem].copy_(lin.bias.detach()[full * 16:])
+            e["fc2_w"][:, :H].copy_(blk.ffn.fc2.weight.detach())
+        self.fin_w.copy_(model.final_layer.linear.weight.detach())
+        self.fin_b = f32(model.final_layer.linear.bias)
+
+    @staticmethod
+    def _ada_linears(model):
+        return [b.adaLN_modulation[1] for b in model.blocks] + [model.final_layer.adaLN_modulation[1]]
+
+    def _ada_slice(self, i):
+        L = len(self.blocks)
+        return (6 * self.D * i, 6 * self.D) if i < L else (6 * self.D * L, 2 * self.D)
+
+    def shadow_specs(self, model):
+        """[(parameter, shadow tensor, row_len, shadow_ld, pack_off)]: where the fused optimizer kernel writes the kernel-layout copy of each
+        parameter that is not read in place (fitb200_adam_tensor.shadow)."""
+        D, Hp = self.D, self.Hp
+        specs = []
+        for i, lin in enumerate(self._ada_linears(model)):
+            o, n = self._ada_slice(i)
+            specs.append((lin.weight, self.ada_w[o:o + n], D, D, -1))
+            specs.append((lin.bias, self.ada_b[o:o + n], 1, 1, -1))
+        for blk, e in zip(model.blocks, self.blocks):
+            specs.append((blk.attn.qkv.weight, e["qkv_w"], D, D, -1))
+            specs.append((blk.attn.proj.weight, e["proj_w"], D, D, -1))
+            specs.append((blk.ffn.fc1_g.weight, e["fc1_w"], D, D, 0))
+            specs.append((blk.ffn.fc1_x.weight, e["fc1_w"], D, D, 16))
+            specs.append((blk.ffn.fc1_g.bias, e["fc1_b"], 1, 1, 0))
+            specs.append((blk.ffn.fc1_x.bias, e["fc1_b"], 1, 1, 16))
+            specs.append((blk.ffn.fc2.weight, e["fc2_w"], self.H, Hp, -1))
+        specs.append((model.final_layer.linear.weight, self.fin_w, D, D, -1))
+        return specs
 
 
 class Saved:
@@ -93,15 +133,24 @@ class FiTTrainEngine:
     def act(self):
         return torch.bfloat16 if self.precision == "bf16" else torch.float32
 
+    def _key(self):
+        return (self.precision,) + tuple((p.data_ptr(), p._version) for p in self.model.parameters())
+
     def weights(self) -> TrainWeights:
-        params = list(self.model.parameters())
-        key = (self.precision,) + tuple((p.data_ptr(), p._version) for p in params)
-        if self._w is None or key != self._w_key:
-            if not params[0].is_cuda:
+        key = self._key()
+        if self._w is None:
+            if not next(self.model.parameters()).is_cuda:
                 raise RuntimeError("fit_b200: the model must live on a CUDA device (no CPU fallback)")
             self._w = TrainWeights(self.model, self.precision)
-            self._w_key = key
+        elif key != self._w_key:
+            self._w.refresh(self.model)     # same buffers, new contents
+        self._w_key = key
         return self._w
+
+    def adopt_parameter_versions(self):
+        """Called by the attached optimizer after a step whose kernel wrote the kernel-layout copies itself: the buffers are current."""
+        if self._w is not None:
+            self._w_key = self._key()
 
     # ------------------------------------------------------------------------------------------ forward
     def forward(self, x: Tensor, t: Tensor, y: Tensor, pos: Tensor, mask: Tensor, train: bool = True):
@@ -152,6 +201,7 @@ class FiTTrainEngine:
         ops.gemm(S.silu_c, W.ada_w, W.ada_b, S.mod, EPI_BIAS)
         S.blocks = []
         for i in range(L):
+          with rng(f"train/fwd/block/{i}"):
             e = W.blocks[i]
             sh1, sc1, g1, sh2, sc2, g2 = [S.mod[:, (6 * i + k) * D:(6 * i + k + 1) * D] for k in range(6)]
             b = Saved()
@@ -256,6 +306,7 @@ class FiTTrainEngine:
 
         # ---- blocks, last to first (fit.py:326-337)
         for i in reversed(range(L)):
+          with rng(f"train/bwd/block/{i}"):
             e, b = W.blocks[i], S.blocks[i]
             pre = f"blocks.{i}."
             mv = [S.mod[:, (6 * i + k) * D:(6 * i + k + 1) * D] for k in range(6)]

@@ -23,7 +23,9 @@ ADAM_CHUNK = 16384  # FITB200_ADAM_CHUNK
 
 class _AdamTensor(C.Structure):
     """Mirror of fitb200_adam_tensor (include/fit_b200.h)."""
-    _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("ema", C.c_void_p), ("numel", C.c_int64)]
+    _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("ema", C.c_void_p), ("numel", C.c_int64),
+                ("shadow", C.c_void_p), ("shadow_ld", C.c_int64), ("shadow_dtype", C.c_int32), ("row_len", C.c_int32),
+                ("pack_off", C.c_int32), ("reserved_", C.c_int32)]
 
 
 class FusedAdamWEMA:
@@ -46,10 +48,26 @@ class FusedAdamWEMA:
         self.ema_params = tuple(p.detach().clone() for p in self.params) if ema_decay is not None else ()
         self._table = None
         self._table_key = None
+        self._engine = None            # FiTTrainEngine whose kernel-layout weight buffers this optimizer keeps current
+        self._shadows = {}             # parameter index -> (shadow tensor, row_len, shadow_ld, pack_off)
+
+    def attach_engine(self, engine):
+        """Let the step kernel write the bf16 / packed copies of the updated parameters into ``engine``'s weight buffers
+        (``FiTTrainEngine.weights().shadow_specs``), so the training forward of the next step starts without re-casting anything."""
+        W = engine.weights()
+        index = {id(p): i for i, p in enumerate(self.params)}
+        self._shadows = {}
+        for p, shadow, row_len, shadow_ld, pack_off in W.shadow_specs(engine.model):
+            if id(p) in index:
+                self._shadows[index[id(p)]] = (shadow, row_len, shadow_ld, pack_off)
+        self._engine = engine
+        self._table = None
+        return self
 
     # ------------------------------------------------------------------ tables
     def _build_table(self, grads: List[torch.Tensor]):
-        key = tuple(g.data_ptr() for g in grads) + tuple(p.data_ptr() for p in self.params)
+        key = tuple(g.data_ptr() for g in grads) + tuple(p.data_ptr() for p in self.params) + tuple(
+            (i, sh[0].data_ptr()) for i, sh in sorted(self._shadows.items()))
         if self._table is not None and key == self._table_key:
             return
         dev = self.params[0].device
@@ -59,6 +77,11 @@ class FusedAdamWEMA:
             arr[i].p, arr[i].g, arr[i].m, arr[i].v = p.data_ptr(), g.data_ptr(), self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr()
             arr[i].ema = self.ema_params[i].data_ptr() if self.ema_params else 0
             arr[i].numel = p.numel()
+            arr[i].shadow, arr[i].row_len, arr[i].shadow_ld, arr[i].pack_off = 0, 1, 1, -1
+            if i in self._shadows:
+                sh, row_len, shadow_ld, pack_off = self._shadows[i]
+                arr[i].shadow, arr[i].shadow_dtype = sh.data_ptr(), L.dtype_code(sh)
+                arr[i].row_len, arr[i].shadow_ld, arr[i].pack_off = row_len, shadow_ld, pack_off
             if any(int(x or 0) % 16 for x in (arr[i].p, arr[i].g, arr[i].m, arr[i].v, arr[i].ema)):
                 raise RuntimeError("fit_b200.optim: parameter / gradient / state tensors must be 16-byte aligned")
             for first in range(0, p.numel(), ADAM_CHUNK):
@@ -97,6 +120,8 @@ class FusedAdamWEMA:
         L.check(L.lib().fitb200_adamw_ema_step(L.ptr(tab), L.ptr(chunks), n_chunks, self.lr, b1, b2, self.eps, self.weight_decay, bc1, bc2_sqrt,
                                                self.ema_decay if do_ema else -1.0, L.stream_ptr()), "adamw_ema_step")
         self.bump_versions()
+        if self._engine is not None:
+            self._engine.adopt_parameter_versions()
 
     def bump_versions(self):
         """The kernel wrote the parameters behind autograd's back: bump their version counters so that the weight caches keyed by

@@ -17,6 +17,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import ops
+from ._nvtx import rng
 
 Tensor = torch.Tensor
 
@@ -65,12 +66,14 @@ class CFGSampler:
     def _step(self):
         d, m = self.diffusion, self.model
         tb = d._tables(self.device)
-        ops.gather_i64(d._map_tensor(self.device), self.t_idx, self.t_model)
-        m.engine.forward(self.x, self.t_model, self.y, self.pos, self.mask, train=False, rows=2 * self.B, out=self.raw)
-        ops.philox_normal(self.noise, self.seed, self.t_idx, self.row_offset_dev)
-        ops.cfg_step(self.x, self.raw, self.noise, self.t_idx[: self.B], tb["coef"], cfg_pairs=self.B, cfg_scale=self.cfg_scale,
-                     ddim=(self.mode == "ddim"), eta=self.eta, flags=d._flags(self.clip), sample=self.x)
-        ops.add_i64(self.t_idx, -1)
+        with rng("sample/model"):
+            ops.gather_i64(d._map_tensor(self.device), self.t_idx, self.t_model)
+            m.engine.forward(self.x, self.t_model, self.y, self.pos, self.mask, train=False, rows=2 * self.B, out=self.raw)
+        with rng("sample/cfg+step"):
+            ops.philox_normal(self.noise, self.seed, self.t_idx, self.row_offset_dev)
+            ops.cfg_step(self.x, self.raw, self.noise, self.t_idx[: self.B], tb["coef"], cfg_pairs=self.B, cfg_scale=self.cfg_scale,
+                         ddim=(self.mode == "ddim"), eta=self.eta, flags=d._flags(self.clip), sample=self.x)
+            ops.add_i64(self.t_idx, -1)
 
     def kernels_per_step(self) -> int:
         """Number of libfit_b200 kernel launches in one step: 7 per block (un-fused: 2 ln_modulate + 4 GEMMs + attention; LN prologue: 2 small

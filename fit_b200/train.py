@@ -24,6 +24,14 @@ def _train_engine(model) -> FiTTrainEngine:
     return eng
 
 
+def attach_optimizer(model, optimizer):
+    """``FusedAdamWEMA`` <-> training engine: the optimizer kernel writes the bf16 / packed operand copies of the parameters it updates
+    straight into the engine's weight buffers (FiT/train.py:215-217 runs AdamW on fp32 masters and autocast re-casts them every forward;
+    here the cast rides in the optimizer pass).  Without it the engine re-fills its buffers whenever a parameter version changes."""
+    optimizer.attach_engine(_train_engine(model))
+    return optimizer
+
+
 class _FiTFunction(torch.autograd.Function):
     """One autograd node for the whole network: forward keeps the activations, backward returns every parameter gradient."""
 

@@ -299,6 +299,16 @@ typedef struct fitb200_adam_tensor {
   float* v;
   float* ema;
   int64_t numel;
+  /* optional kernel-layout copy of the UPDATED parameter, written in the same pass (NULL = none): the bf16 (or packed fp32) operand the
+   * GEMMs read, so that nothing re-casts / re-packs 675 M parameters after every step.  p is viewed as [numel / row_len, row_len];
+   * element (row, col) goes to shadow[srow * shadow_ld + col] with srow = row (pack_off < 0) or (row / 16) * 32 + pack_off + row % 16
+   * (pack_off = 0 / 16: the fc1_g / fc1_x halves of the packed SwiGLU weight and bias, FITB200_EPI_SWIGLU). */
+  void* shadow;
+  int64_t shadow_ld;
+  int32_t shadow_dtype; /* FITB200_BF16 or FITB200_F32 */
+  int32_t row_len;
+  int32_t pack_off;
+  int32_t reserved_;
 } fitb200_adam_tensor;
 int fitb200_adamw_ema_step(const fitb200_adam_tensor* tensors, const int32_t* chunks, int n_chunks, double lr, double beta1, double beta2,
                            double eps, double weight_decay, double bias_correction1, double bias_correction2_sqrt, double ema_decay,

@@ -128,3 +128,50 @@ def test_optimizer_resume_matches_uninterrupted_run(layout):
         assert torch.equal(a.detach(), c.detach())
     for a, c in zip(oa.ema_params, oc.ema_params):
         assert torch.equal(a, c)
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+@pytest.mark.parametrize("mlp_ratio", [4.0, 3.7])   # 3.7: hidden width 355 -> padded to 368 (the FiT-L case: 2730 -> 2736)
+def test_optimizer_keeps_engine_weight_buffers_current(precision, mlp_ratio):
+    """attach_optimizer: the step kernel writes the bf16 / packed copies of the updated parameters into the training engine's weight buffers
+    (fitb200_adam_tensor.shadow).  After a step they are bit-identical to a fresh re-pack of the new parameters, the engine does not refill
+    them, and a training step through them matches a model rebuilt from the same parameters."""
+    from fit_b200.engine_train import TrainWeights
+    from fit_b200.models.fit import FiT
+    from fit_b200.optim import FusedAdamWEMA
+    from fit_b200.train import _train_engine, attach_optimizer, masked_mse_loss
+    from oracle import fit_oracle as fo
+    from oracle import synth
+    cfg = dict(patch_size=2, in_channels=4, hidden_size=144, depth=2, num_heads=2, mlp_ratio=mlp_ratio, class_dropout_prob=0.1, num_classes=10,
+               learn_sigma=False)
+    sd = fo.random_state_dict(cfg, seed=3)
+    m = FiT(**cfg, precision=precision)
+    m.load_state_dict(sd)
+    m = m.cuda().train()
+    m.y_embedder.dropout_prob = 0.0
+    x, t, y, pos, mask, target = synth.mixed_batch(cfg, [(16, 16), (8, 32)], 64, seed=5, rope_dim=72)
+    opt = attach_optimizer(m, FusedAdamWEMA(m.parameters(), lr=1e-2, ema_decay=0.99))
+    eng = _train_engine(m)
+    refills = []
+    orig = TrainWeights.refresh
+    TrainWeights.refresh = lambda self, model: (refills.append(1), orig(self, model))[1]
+    try:
+        for _ in range(2):
+            for p in m.parameters():
+                p.grad = None
+            loss = masked_mse_loss(m(x.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda(), train=True), target.cuda(), mask.cuda())
+            loss.backward()
+            opt.step()
+        W = eng.weights()
+        assert not refills, "the engine re-packed its weights although the optimizer keeps them current"
+    finally:
+        TrainWeights.refresh = orig
+    fresh = TrainWeights(m, precision)
+    assert torch.equal(W.ada_w, fresh.ada_w) and torch.equal(W.ada_b, fresh.ada_b) and torch.equal(W.fin_w, fresh.fin_w)
+    for a, b in zip(W.blocks, fresh.blocks):
+        for k in ("qkv_w", "proj_w", "fc1_w", "fc1_b", "fc2_w", "qkv_b", "proj_b", "fc2_b"):
+            assert torch.equal(a[k], b[k]), k
+    # a parameter change behind the optimizer's back (load_state_dict) still refills
+    m.load_state_dict({k: v.cuda() for k, v in sd.items()})
+    W2 = eng.weights()
+    assert W2 is W and torch.equal(W2.blocks[0]["qkv_w"].float(), m.blocks[0].attn.qkv.weight.detach().to(W2.wdt).float())
