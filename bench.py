@@ -362,7 +362,7 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
     import torch.distributed as dist
     from fit_b200 import _lib as L
     from fit_b200.optim import FusedAdamWEMA
-    from fit_b200.train import GradSync, attach_optimizer, masked_mse_loss
+    from fit_b200.train import CapturedTrainStep, GradSync, masked_mse_loss
     from fit_b200.rope import precompute_freqs_cis_2d
     D, Hd, Ld, heads = MODELS[args.model]
     T, d = 256, D // heads
@@ -376,17 +376,13 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
     pos = torch.tensor(precompute_freqs_cis_2d(d, 16, 16, max_length=256), dtype=torch.float32)[None].expand(samples, T, d).contiguous().to(dev)
     mask = torch.ones(samples, T, dtype=torch.bool, device=dev)
     sync = GradSync().attach(model) if world > 1 else None
-    opt = attach_optimizer(model, FusedAdamWEMA(model.parameters(), lr=1e-4, weight_decay=0.0, ema_decay=0.9999))
+    opt = FusedAdamWEMA(model.parameters(), lr=1e-4, weight_decay=0.0, ema_decay=0.9999)
+    # one GPU: the whole step (forward, loss, backward, AdamW/EMA) is ONE replayed CUDA graph; data parallel: issued eagerly, the per-block
+    # all-reduces overlap the backward on a side stream (GradSync.finish runs inside the autograd node's backward)
+    cstep = CapturedTrainStep(model, opt)
 
-    def step(do_opt=True):
-        for p in model.parameters():
-            p.grad = None
-        out = model(x, t, y, pos, mask, train=True)
-        loss = masked_mse_loss(out, tgt, mask)
-        loss.backward()          # GradSync.finish runs inside the autograd node's backward
-        if do_opt:
-            opt.step()
-        return loss
+    def step():
+        return cstep(x, t, y, pos, mask, tgt)
 
     def timed(fn, n):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -405,7 +401,9 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
            "train_samples_s": samples * world / (ms * 1e-3),
            "train_tflops_per_gpu": 3 * samples * forward_flops(D, Hd, Ld, T) / (ms * 1e-3) / 1e12,
            "train_loss": float(loss.detach()),
-           "train_step": "fwd + bwd + per-block NCCL all-reduce (AVG, fp32, overlapped) + fused AdamW/EMA; 3 x forward FLOPs counted"}
+           "train_graph": cstep.captures > 0,
+           "train_step": ("fwd + bwd + fused AdamW/EMA replayed as one CUDA graph" if cstep.captures > 0 else
+                          "fwd + bwd + per-block NCCL all-reduce (AVG, fp32, overlapped) + fused AdamW/EMA, issued eagerly") + "; 3 x forward FLOPs counted"}
     if sync is not None:
         with sync.no_sync():
             ms_local = timed(step, iters)
@@ -428,7 +426,7 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
         object.__setattr__(model, "_grad_sync", None)
         n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
         L.check(L.lib().fitb200_set_sm_limit(n_sm), "set_sm_limit")   # GradSync reserved SMs for NCCL: give them back
-    del opt
+    del cstep, opt
     for p in model.parameters():
         p.grad = None
     model.train(was_training)

@@ -10,8 +10,32 @@ namespace fitb200 {
 
 struct AdamScalars { float step, decay_p, omb1, beta2, omb2, bc2_sqrt, eps, ema_decay, ome; };
 
+// derived scalars in double, as torch forms them (step_size = lr / bc1, value = 1 - beta2, alpha = 1 - decay), then one rounding to fp32
+__host__ __device__ inline AdamScalars adam_scalars(double lr, double beta1, double beta2, double eps, double weight_decay, double bc1,
+                                                     double bc2_sqrt, double ema_decay) {
+  AdamScalars sc;
+  sc.step = (float)(lr / bc1); sc.decay_p = (float)(1.0 - lr * weight_decay); sc.omb1 = (float)(1.0 - beta1);
+  sc.beta2 = (float)beta2; sc.omb2 = (float)(1.0 - beta2); sc.bc2_sqrt = (float)bc2_sqrt; sc.eps = (float)eps;
+  sc.ema_decay = (float)ema_decay; sc.ome = (float)(1.0 - ema_decay);
+  return sc;
+}
+
+// DEV: the step-dependent scalars come from DEVICE memory (hyper = {lr, beta1, beta2, eps, weight_decay, ema_decay}, step_dev = the number
+// of this step, every_n = EMA period), so that one captured CUDA graph serves every step (torch.optim's capturable=True)
+template <bool DEV>
 __global__ void __launch_bounds__(256) adamw_ema_kernel(const fitb200_adam_tensor* __restrict__ tensors, const int32_t* __restrict__ chunks,
-                                                        const AdamScalars sc) {
+                                                        const AdamScalars sc_host, const double* __restrict__ hyper,
+                                                        const int64_t* __restrict__ step_dev, int every_n) {
+  __shared__ AdamScalars sc_sh;
+  if (DEV) {
+    if (threadIdx.x == 0) {
+      const double lr = hyper[0], b1 = hyper[1], b2 = hyper[2], t = (double)step_dev[0];
+      const bool ema_now = hyper[5] >= 0.0 && (step_dev[0] - 1) % (every_n > 0 ? every_n : 1) == 0;   // FiT/ema.py:252-257
+      sc_sh = adam_scalars(lr, b1, b2, hyper[3], hyper[4], 1.0 - pow(b1, t), sqrt(1.0 - pow(b2, t)), ema_now ? hyper[5] : -1.0);
+    }
+    __syncthreads();
+  }
+  const AdamScalars sc = DEV ? sc_sh : sc_host;
   const int ti = chunks[2 * blockIdx.x], first = chunks[2 * blockIdx.x + 1];
   const fitb200_adam_tensor t = tensors[ti];
   const int64_t base = (int64_t)first;
@@ -127,12 +151,17 @@ extern "C" int fitb200_adamw_ema_step(const fitb200_adam_tensor* tensors, const 
   FITB200_CHECK_ARG(tensors && chunks && n_chunks >= 0, "adamw_ema_step: null table");
   FITB200_CHECK_ARG(bias_correction1 > 0. && bias_correction2_sqrt > 0., "adamw_ema_step: bias corrections must be positive (step >= 1)");
   if (n_chunks == 0) return FITB200_OK;
-  // derived scalars in double, as torch forms them (step_size = lr / bc1, value = 1 - beta2, alpha = 1 - decay), then one rounding to fp32
-  AdamScalars sc;
-  sc.step = (float)(lr / bias_correction1); sc.decay_p = (float)(1.0 - lr * weight_decay); sc.omb1 = (float)(1.0 - beta1);
-  sc.beta2 = (float)beta2; sc.omb2 = (float)(1.0 - beta2); sc.bc2_sqrt = (float)bias_correction2_sqrt; sc.eps = (float)eps;
-  sc.ema_decay = (float)ema_decay; sc.ome = (float)(1.0 - ema_decay);
-  adamw_ema_kernel<<<n_chunks, 256, 0, (cudaStream_t)stream>>>(tensors, chunks, sc);
+  const AdamScalars sc = adam_scalars(lr, beta1, beta2, eps, weight_decay, bias_correction1, bias_correction2_sqrt, ema_decay);
+  adamw_ema_kernel<false><<<n_chunks, 256, 0, (cudaStream_t)stream>>>(tensors, chunks, sc, nullptr, nullptr, 1);
   FITB200_CHECK_LAUNCH("adamw_ema_step");
+  return FITB200_OK;
+}
+
+extern "C" int fitb200_adamw_ema_step_dev(const fitb200_adam_tensor* tensors, const int32_t* chunks, int n_chunks, const double* hyper,
+                                          const int64_t* step, int every_n_steps, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(tensors && chunks && n_chunks >= 0 && hyper && step && every_n_steps >= 1, "adamw_ema_step_dev: bad arguments");
+  if (n_chunks == 0) return FITB200_OK;
+  adamw_ema_kernel<true><<<n_chunks, 256, 0, (cudaStream_t)stream>>>(tensors, chunks, AdamScalars{}, hyper, step, every_n_steps);
+  FITB200_CHECK_LAUNCH("adamw_ema_step_dev");
   return FITB200_OK;
 }

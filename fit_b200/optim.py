@@ -48,6 +48,11 @@ class FusedAdamWEMA:
         self.ema_params = tuple(p.detach().clone() for p in self.params) if ema_decay is not None else ()
         self._table = None
         self._table_key = None
+        # capturable: the step number and the hyper-parameters live in device memory and the kernel derives the bias corrections itself, so
+        # a CUDA graph that contains step() can be replayed for every step (fit_b200.train.CapturedTrainStep); like torch.optim's capturable
+        self.capturable = False
+        self._step_dev = None
+        self._hyper_dev = None
         self._engine = None            # FiTTrainEngine whose kernel-layout weight buffers this optimizer keeps current
         self._shadows = {}             # parameter index -> (shadow tensor, row_len, shadow_ld, pack_off)
 
@@ -86,8 +91,13 @@ class FusedAdamWEMA:
                 raise RuntimeError("fit_b200.optim: parameter / gradient / state tensors must be 16-byte aligned")
             for first in range(0, p.numel(), ADAM_CHUNK):
                 chunks += [i, first]
-        raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone()
-        self._table = (raw.to(dev), torch.tensor(chunks, dtype=torch.int32).to(dev), len(chunks) // 2)
+        # pinned staging + asynchronous copies: legal inside a CUDA-graph capture (CapturedTrainStep); the staging tensors stay alive with the table
+        raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone().pin_memory()
+        chk = torch.tensor(chunks, dtype=torch.int32).pin_memory()
+        raw_d, chk_d = torch.empty(raw.shape, dtype=torch.uint8, device=dev), torch.empty(chk.shape, dtype=torch.int32, device=dev)
+        raw_d.copy_(raw, non_blocking=True)
+        chk_d.copy_(chk, non_blocking=True)
+        self._table = (raw_d, chk_d, len(chunks) // 2, raw, chk)
         self._table_key = key
 
     # ------------------------------------------------------------------ torch.optim-like API
@@ -110,15 +120,52 @@ class FusedAdamWEMA:
                 raise RuntimeError("fit_b200.optim: gradients must be contiguous fp32")
             grads.append(g)
         self._build_table(grads)
+        if self.capturable:
+            return self._step_capturable()
         self.step_count += 1
         b1, b2 = self.betas
         bc1 = 1.0 - b1 ** self.step_count
         bc2_sqrt = math.sqrt(1.0 - b2 ** self.step_count)
         # FiT/ema.py:252-257: the EMA moves when (step index before increment) % every_n_steps == 0
         do_ema = self.ema_decay is not None and (self.step_count - 1) % self.every_n_steps == 0
-        tab, chunks, n_chunks = self._table
+        tab, chunks, n_chunks = self._table[:3]
         L.check(L.lib().fitb200_adamw_ema_step(L.ptr(tab), L.ptr(chunks), n_chunks, self.lr, b1, b2, self.eps, self.weight_decay, bc1, bc2_sqrt,
                                                self.ema_decay if do_ema else -1.0, L.stream_ptr()), "adamw_ema_step")
+        self.bump_versions()
+        if self._engine is not None:
+            self._engine.adopt_parameter_versions()
+
+    def sync_device_state(self):
+        """(Re)write the device-side step number and hyper-parameters from the host-side values (after construction, load_state_dict, or an
+        lr change).  Not capturable itself: call it outside the graph."""
+        dev = self.params[0].device
+        if self._step_dev is None:
+            self._step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+            self._hyper_dev = torch.zeros(6, dtype=torch.float64, device=dev)
+        self._step_dev.fill_(self.step_count)
+        self._hyper_dev.copy_(torch.tensor([self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                                            -1.0 if self.ema_decay is None else self.ema_decay], dtype=torch.float64))
+
+    def _step_capturable(self):
+        if self._step_dev is None:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("fit_b200.optim: run one eager step (or sync_device_state()) before capturing a capturable optimizer")
+            self.sync_device_state()
+        from . import ops
+        ops.add_i64(self._step_dev, 1)
+        tab, chunks, n_chunks = self._table[:3]
+        L.check(L.lib().fitb200_adamw_ema_step_dev(L.ptr(tab), L.ptr(chunks), n_chunks, L.ptr(self._hyper_dev), L.ptr(self._step_dev),
+                                                   self.every_n_steps, L.stream_ptr()), "adamw_ema_step_dev")
+        if not torch.cuda.is_current_stream_capturing():   # a capture records the launch; the replays are counted by note_external_step
+            self.step_count += 1
+        self.bump_versions()
+        if self._engine is not None:
+            self._engine.adopt_parameter_versions()
+
+    def note_external_step(self):
+        """A captured CUDA graph replayed this optimizer's step kernel (fit_b200.train.CapturedTrainStep): advance the host-side step count
+        and the parameter version counters as ``step`` would have."""
+        self.step_count += 1
         self.bump_versions()
         if self._engine is not None:
             self._engine.adopt_parameter_versions()
@@ -184,3 +231,5 @@ class FusedAdamWEMA:
                 raise ValueError(f"EMA state holds {len(sd['ema'])} tensors, the optimizer has {len(self.ema_params)} parameters")
             for e, src in zip(self.ema_params, sd["ema"]):
                 e.copy_(src)
+        if self._step_dev is not None:
+            self.sync_device_state()

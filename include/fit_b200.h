@@ -314,6 +314,13 @@ int fitb200_adamw_ema_step(const fitb200_adam_tensor* tensors, const int32_t* ch
                            double eps, double weight_decay, double bias_correction1, double bias_correction2_sqrt, double ema_decay,
                            fitb200_stream_t stream);
 
+/* The same step with every step-dependent scalar read from DEVICE memory, so that a captured CUDA graph of the training step can be replayed
+ * for every step (the capturable=True mode of torch.optim.AdamW): hyper = device double[6] {lr, beta1, beta2, eps, weight_decay, ema_decay
+ * (< 0: no EMA)}; step = device int64[1], the 1-based number of THIS step (the caller increments it first, e.g. fitb200_add_i64); the bias
+ * corrections 1 - beta^step are formed in double in the kernel; the EMA moves when (step - 1) % every_n_steps == 0 (FiT/ema.py:252-257). */
+int fitb200_adamw_ema_step_dev(const fitb200_adam_tensor* tensors, const int32_t* chunks, int n_chunks, const double* hyper, const int64_t* step,
+                               int every_n_steps, fitb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

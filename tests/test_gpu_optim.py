@@ -175,3 +175,72 @@ def test_optimizer_keeps_engine_weight_buffers_current(precision, mlp_ratio):
     m.load_state_dict({k: v.cuda() for k, v in sd.items()})
     W2 = eng.weights()
     assert W2 is W and torch.equal(W2.blocks[0]["qkv_w"].float(), m.blocks[0].attn.qkv.weight.detach().to(W2.wdt).float())
+
+
+def test_capturable_optimizer_matches_host_scalar_path():
+    """capturable=True (step number and hyper-parameters in device memory, bias corrections formed in the kernel) against the host-scalar
+    path over several steps, incl. the every_n_steps EMA rule and an lr change through sync_device_state()."""
+    from fit_b200.optim import FusedAdamWEMA
+    sizes = [5, 1152, 16385, 40000]
+    init = _mk(sizes, 1)
+    pa = [torch.nn.Parameter(p.clone().cuda()) for p in init]
+    pb = [torch.nn.Parameter(p.clone().cuda()) for p in init]
+    a = FusedAdamWEMA(pa, lr=1e-3, weight_decay=0.01, ema_decay=0.99, every_n_steps=2)
+    b = FusedAdamWEMA(pb, lr=1e-3, weight_decay=0.01, ema_decay=0.99, every_n_steps=2)
+    b.capturable = True
+    for step in range(5):
+        if step == 3:
+            a.lr = b.lr = 5e-4
+            b.sync_device_state()
+        grads = _mk(sizes, 200 + step)
+        for p, q, g in zip(pa, pb, grads):
+            p.grad, q.grad = g.clone().cuda(), g.clone().cuda()
+        a.step(); b.step()
+        for i in range(len(sizes)):
+            torch.testing.assert_close(pb[i].detach(), pa[i].detach(), rtol=1e-6, atol=1e-9)
+            torch.testing.assert_close(b.ema_params[i], a.ema_params[i], rtol=1e-6, atol=1e-9)
+    assert a.step_count == b.step_count == 5 and int(b._step_dev) == 5
+
+
+def test_captured_train_step_matches_eager_steps():
+    """CapturedTrainStep (forward + loss + backward + AdamW/EMA as one replayed CUDA graph) against the same steps issued eagerly: same
+    parameters and EMA after 4 steps on changing batches (atomically accumulated bias / gate gradients make the two runs differ by fp32
+    summation order only), ONE capture, and the parameter version counters advance so that the sampling engine repacks."""
+    from fit_b200.models.fit import FiT
+    from fit_b200.optim import FusedAdamWEMA
+    from fit_b200.train import CapturedTrainStep, attach_optimizer, masked_mse_loss
+    from oracle import fit_oracle as fo
+    from oracle import synth
+    cfg = dict(patch_size=2, in_channels=4, hidden_size=144, depth=2, num_heads=2, mlp_ratio=4.0, class_dropout_prob=0.1, num_classes=10,
+               learn_sigma=False)
+    sd = fo.random_state_dict(cfg, seed=3)
+    models = []
+    for _ in range(2):
+        m = FiT(**cfg, precision="bf16")
+        m.load_state_dict(sd)
+        m = m.cuda().train()
+        m.y_embedder.dropout_prob = 0.0
+        models.append(m)
+    eager, graphed = models
+    oe = attach_optimizer(eager, FusedAdamWEMA(eager.parameters(), lr=1e-3, ema_decay=0.99))
+    og = FusedAdamWEMA(graphed.parameters(), lr=1e-3, ema_decay=0.99)
+    step = CapturedTrainStep(graphed, og)
+    losses = []
+    for k in range(4):
+        x, t, y, pos, mask, target = [b.cuda() for b in synth.mixed_batch(cfg, [(16, 16), (8, 32)], 64, seed=20 + k, rope_dim=72)]
+        for p in eager.parameters():
+            p.grad = None
+        le = masked_mse_loss(eager(x, t, y, pos, mask, train=True), target, mask)
+        le.backward()
+        oe.step()
+        v0 = next(graphed.parameters())._version
+        lg = step(x, t, y, pos, mask, target)
+        losses.append((float(le), float(lg)))
+        assert next(graphed.parameters())._version > v0
+    assert step.captures == 1 and og.step_count == 4
+    for le, lg in losses:
+        assert abs(le - lg) < 2e-3 * abs(le)
+    for (n, p), q in zip(eager.named_parameters(), graphed.parameters()):
+        torch.testing.assert_close(q.detach(), p.detach(), rtol=2e-3, atol=2e-5, msg=n)
+    for e1, e2 in zip(oe.ema_params, og.ema_params):
+        torch.testing.assert_close(e2, e1, rtol=2e-3, atol=2e-5)
