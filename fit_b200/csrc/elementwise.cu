@@ -4,6 +4,8 @@
 // All HBM-bound: one pass over the data, 16-byte accesses, fp32 math.
 #include <cstdarg>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace fitb200 {
@@ -46,7 +48,8 @@ __global__ void mask_to_kvlen_kernel(const uint8_t* __restrict__ mask, int R, in
 // --------------------------------------------------------------------------------------------
 // patchify + x_embedder.  CTA: TOK tokens x 128 output columns.
 // --------------------------------------------------------------------------------------------
-constexpr int EMB_TOK = 32;
+constexpr int EMB_TOK = 16;
+constexpr int EMB_COLS = 4;   // output columns per thread: 8-byte (bf16) / 16-byte (fp32) stores, a warp writes 256 / 512 contiguous bytes per token
 
 template <typename OutT>
 __global__ void __launch_bounds__(128) embed_tokens_kernel(const float* __restrict__ x, int nchw, int R, int R_src, int C,
@@ -76,27 +79,38 @@ __global__ void __launch_bounds__(128) embed_tokens_kernel(const float* __restri
     xs[i] = v;
   }
   __syncthreads();
-  const int j = blockIdx.y * 128 + threadIdx.x;
-  if (j >= D) return;
-  float acc[EMB_TOK];
-  const float bj = b[j];
+  const int j0 = (blockIdx.y * 128 + threadIdx.x) * EMB_COLS;   // D % 4 == 0 (checked on the host)
+  if (j0 >= D) return;
+  float acc[EMB_TOK][EMB_COLS];
+  const float4 b4 = *reinterpret_cast<const float4*>(b + j0);
 #pragma unroll
-  for (int t = 0; t < EMB_TOK; ++t) acc[t] = bj;
+  for (int t = 0; t < EMB_TOK; ++t) { acc[t][0] = b4.x; acc[t][1] = b4.y; acc[t][2] = b4.z; acc[t][3] = b4.w; }
   for (int k0 = 0; k0 < K; k0 += 4) {
-    float4 wv = *reinterpret_cast<const float4*>(w + (size_t)j * K + k0);
+    float4 wv[EMB_COLS];
+#pragma unroll
+    for (int c = 0; c < EMB_COLS; ++c) wv[c] = *reinterpret_cast<const float4*>(w + (size_t)(j0 + c) * K + k0);
 #pragma unroll
     for (int t = 0; t < EMB_TOK; ++t) {
-      const float* xr = xs + t * K + k0;
-      acc[t] = fmaf(wv.x, xr[0], acc[t]);
-      acc[t] = fmaf(wv.y, xr[1], acc[t]);
-      acc[t] = fmaf(wv.z, xr[2], acc[t]);
-      acc[t] = fmaf(wv.w, xr[3], acc[t]);
+      const float4 xv = *reinterpret_cast<const float4*>(xs + t * K + k0);   // the same address for the whole warp: a broadcast
+#pragma unroll
+      for (int c = 0; c < EMB_COLS; ++c) {
+        float a = acc[t][c];
+        a = fmaf(wv[c].x, xv.x, a); a = fmaf(wv[c].y, xv.y, a); a = fmaf(wv[c].z, xv.z, a); a = fmaf(wv[c].w, xv.w, a);
+        acc[t][c] = a;
+      }
     }
   }
 #pragma unroll
   for (int t = 0; t < EMB_TOK; ++t) {
     long tok = tok0 + t;
-    if (tok < ntok) out[(size_t)tok * D + j] = from_f32<OutT>(acc[t]);
+    if (tok < ntok) {
+      if constexpr (sizeof(OutT) == 2) {
+        uint2 o; o.x = pack_bf16x2(acc[t][0], acc[t][1]); o.y = pack_bf16x2(acc[t][2], acc[t][3]);
+        *reinterpret_cast<uint2*>(out + (size_t)tok * D + j0) = o;
+      } else {
+        *reinterpret_cast<float4*>(out + (size_t)tok * D + j0) = make_float4(acc[t][0], acc[t][1], acc[t][2], acc[t][3]);
+      }
+    }
   }
 }
 
@@ -340,6 +354,106 @@ __global__ void __launch_bounds__(256) final_layer_kernel(const InT* __restrict_
         out[(((size_t)r * C + c) * H + (ih * p + ph)) * W + (iw * p + pw)] = val;
       } else {
         out[(size_t)tok * P + o] = val;
+      }
+    }
+  }
+}
+
+// The same with the [P, D] weight staged ONCE per CTA in shared memory (lane-contiguous float4 layout) and persistent CTAs that walk the
+// tokens two per warp and round: the one-warp-per-token kernel above re-reads the 74 KB weight from L1 / L2 for every token (9.6 GB at the
+// headline shape: 1.03 ms for a 0.3 GB stream = 0.05 of the HBM roofline).  Used when P * D * 4 bytes fit (p = 2: P = 16).
+template <typename InT, int NV>
+__global__ void __launch_bounds__(256, 2) final_layer_smem_kernel(const InT* __restrict__ x, int R, int T, int D,
+                                                                 const float* __restrict__ shift, const float* __restrict__ scale,
+                                                                 long ld_mod, const float* __restrict__ w, const float* __restrict__ b,
+                                                                 int P, float* __restrict__ out, int nchw, int C, int H, int W, int p) {
+  extern __shared__ __align__(16) float4 fl_w4[];   // [P][NV][2][32]: lane l's two float4 of vector (l + 32 i) of output row o
+  const int nvec = D >> 3;
+  for (int idx = threadIdx.x; idx < P * (D >> 2); idx += blockDim.x) {
+    const int o = idx / (D >> 2), q4 = idx - o * (D >> 2);      // q4: float4 index inside row o
+    const int vi = q4 >> 1, hf = q4 & 1;
+    fl_w4[((o * NV + (vi >> 5)) * 2 + hf) * 32 + (vi & 31)] = *reinterpret_cast<const float4*>(w + (size_t)o * D + q4 * 4);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long ntok = (long)R * T;
+  const long nwarps = (long)gridDim.x * 8;
+  const int nw = nchw ? (W / p) : 0;
+  for (long t0 = ((long)blockIdx.x * 8 + warp) * 2; t0 < ntok; t0 += nwarps * 2) {
+    float v[2][NV][8];
+    bool live[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const long tok = t0 + j;
+      live[j] = tok < ntok;
+      const InT* xr = x + (size_t)(live[j] ? tok : t0) * D;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vi = lane + i * 32;
+        if (vi < nvec) {
+          const Vec8<InT> a = Vec8<InT>::load(xr + vi * 8);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[j][i][e] = a.v[e];
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[j][i][e] = 0.f;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const long tok = live[j] ? t0 + j : t0;
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += v[j][i][e];
+      const float mu = warp_sum(s) / (float)D;
+      float q = 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        if (lane + i * 32 < nvec) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { const float d = v[j][i][e] - mu; q = fmaf(d, d, q); }
+        }
+      }
+      const float rstd = rsqrtf(warp_sum(q) / (float)D + 1e-6f);
+      const size_t mrow = (size_t)(tok / T) * ld_mod;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vi = lane + i * 32;
+        if (vi < nvec) {
+          const Vec8<float> sh = Vec8<float>::load(shift + mrow + vi * 8);
+          const Vec8<float> sc = Vec8<float>::load(scale + mrow + vi * 8);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[j][i][e] = fmaf((v[j][i][e] - mu) * rstd, 1.0f + sc.v[e], sh.v[e]);
+        }
+      }
+    }
+    for (int o = 0; o < P; ++o) {
+      float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        if (lane + i * 32 < nvec) {
+          const float4 wa = fl_w4[((o * NV + i) * 2 + 0) * 32 + lane], wb = fl_w4[((o * NV + i) * 2 + 1) * 32 + lane];
+          const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { acc0 = fmaf(v[0][i][e], wv[e], acc0); acc1 = fmaf(v[1][i][e], wv[e], acc1); }
+        }
+      }
+      acc0 = warp_sum(acc0); acc1 = warp_sum(acc1);
+      if (lane < 2 && live[lane]) {
+        const long tok = t0 + lane;
+        const float val = (lane == 0 ? acc0 : acc1) + b[o];
+        if (nchw) {
+          const int r = (int)(tok / T), tk = (int)(tok - (long)r * T);
+          const int ih = tk / nw, iw = tk - ih * nw;
+          const int c = o % C, pp = o / C;
+          const int ph = pp / p, pw = pp - ph * p;
+          out[(((size_t)r * C + c) * H + (ih * p + ph)) * W + (iw * p + pw)] = val;
+        } else {
+          out[(size_t)tok * P + o] = val;
+        }
       }
     }
   }
@@ -606,7 +720,8 @@ int fitb200_embed_tokens_fwd(const float* x, int x_is_nchw, int R, int R_src, in
   const int K = p * p * C;
   FITB200_CHECK_ARG(K % 4 == 0 && K <= 1024, "embed_tokens: p*p*C=%d must be a multiple of 4 and <= 1024", K);
   if (x_is_nchw) FITB200_CHECK_ARG(H % p == 0 && W % p == 0 && (H / p) * (W / p) == T, "embed_tokens: T=%d != (H/p)*(W/p)", T);
-  dim3 grid((unsigned)ceil_div((long)R * T, (long)EMB_TOK), (unsigned)ceil_div(D, 128));
+  FITB200_CHECK_ARG(D % EMB_COLS == 0, "embed_tokens: D=%d must be a multiple of 4", D);
+  dim3 grid((unsigned)ceil_div((long)R * T, (long)EMB_TOK), (unsigned)ceil_div(D, 128 * EMB_COLS));
   size_t smem = (size_t)EMB_TOK * K * sizeof(float);
   FITB200_DISPATCH_ACT(out_dtype, OutT, {
     if (smem > 48 * 1024) cudaFuncSetAttribute(embed_tokens_kernel<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -656,6 +771,27 @@ int fitb200_final_layer_fwd(const void* x, int x_dtype, int R, int T, int D, con
   FITB200_CHECK_ARG(D % 8 == 0 && D <= 32 * 8 * LN_MAXV && ld_mod % 4 == 0, "final_layer: D=%d must be a multiple of 8 and <= %d", D, 32 * 8 * LN_MAXV);
   if (out_nchw) FITB200_CHECK_ARG(p > 0 && C > 0 && P % C == 0 && P == p * p * C && H % p == 0 && W % p == 0 && (H / p) * (W / p) == T, "final_layer: inconsistent unpatchify shape");
   dim3 grid((unsigned)ceil_div((long)R * T, 8L));
+  const int nv = ceil_div(D >> 3, 32);
+  const size_t wbytes = (size_t)P * nv * 2 * 32 * sizeof(float4);
+  static const bool smem_ok = [] { const char* e = getenv("FITB200_FINAL_SMEM"); return !(e && e[0] == '0'); }();
+  if (smem_ok && wbytes <= 100 * 1024 && ((uintptr_t)w & 15) == 0 && (long)R * T >= 4096) {
+    const int ctas = (int)std::min<long>(2L * sm_count(), ceil_div((long)R * T, 16L));
+#define FITB200_FINAL_CASE(NVV)                                                                                                     \
+    case NVV: {                                                                                                                     \
+      FITB200_DISPATCH_ACT(x_dtype, InT, {                                                                                          \
+        auto kern = final_layer_smem_kernel<InT, NVV>;                                                                              \
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wbytes);                                       \
+        kern<<<ctas, 256, wbytes, (cudaStream_t)stream>>>((const InT*)x, R, T, D, shift, scale, ld_mod, w, b, P, out, out_nchw, C, H, W, p); \
+      })                                                                                                                            \
+    } break;
+    switch (nv) {
+      FITB200_FINAL_CASE(1) FITB200_FINAL_CASE(2) FITB200_FINAL_CASE(3) FITB200_FINAL_CASE(4) FITB200_FINAL_CASE(5)
+      default: set_last_error("final_layer: D=%d too wide", D); return FITB200_ERR_UNSUPPORTED;
+    }
+#undef FITB200_FINAL_CASE
+    FITB200_CHECK_LAUNCH("final_layer");
+    return FITB200_OK;
+  }
   FITB200_DISPATCH_ACT(x_dtype, InT, {
     final_layer_kernel<InT><<<grid, 256, 0, (cudaStream_t)stream>>>((const InT*)x, R, T, D, shift, scale, ld_mod, w, b, P, out, out_nchw, C, H, W, p);
   })

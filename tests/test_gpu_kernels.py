@@ -203,6 +203,30 @@ def test_final_layer(ops, xdt, D, H, W, p):
     assert rel_l2(out4, fo.unpatchify(tok, H, W, p, C)) < 1e-5
 
 
+@pytest.mark.parametrize("xdt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("R,D,H,W,p", [(17, 1152, 32, 32, 2), (33, 768, 20, 40, 2), (24, 384, 32, 32, 2), (17, 1024, 64, 64, 4)])
+def test_final_layer_persistent_smem_weight(ops, xdt, R, D, H, W, p):
+    """>= 4096 tokens: the persistent kernel with the [P, D] weight in shared memory (two tokens per warp and round; odd token counts, every
+    FiT width, P = 16 and 64) -- same arithmetic as the one-warp-per-token kernel, which the small shapes above take."""
+    g = torch.Generator().manual_seed(D + R)
+    C = 4
+    T = (H // p) * (W // p)
+    P = p * p * C
+    assert R * T >= 4096
+    x = (torch.randn(R, T, D, generator=g) * 2).to(xdt)
+    mod = torch.randn(R, 2 * D, generator=g) * 0.5
+    w = torch.randn(P, D, generator=g) * 0.05
+    b = torch.randn(P, generator=g)
+    tok = F.linear(fo.modulate(fo.layer_norm(x.float()), mod[:, :D], mod[:, D:]), w, b)
+    modc = mod.cuda()
+    out = torch.empty(R, T, P, device="cuda")
+    ops.final_layer(x.cuda().view(R * T, D), modc[:, :D], modc[:, D:], 2 * D, w.cuda(), b.cuda(), out, R, T, p, C)
+    assert rel_l2(out, tok) < 1e-5
+    out4 = torch.empty(R, C, H, W, device="cuda")
+    ops.final_layer(x.cuda().view(R * T, D), modc[:, :D], modc[:, D:], 2 * D, w.cuda(), b.cuda(), out4, R, T, p, C)
+    assert rel_l2(out4, fo.unpatchify(tok, H, W, p, C)) < 1e-5
+
+
 # ------------------------------------------------------------------------------ attention (family 2)
 def _attn_case(R, T, h, d, lens, seed, nonprefix=False):
     g = torch.Generator().manual_seed(seed)
