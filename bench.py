@@ -395,7 +395,7 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
         return all_max(e0.elapsed_time(e1)) / n
 
     for _ in range(2):
-        loss = step()
+        loss = step().clone()      # (a captured step returns a static tensor: keep the value of the last warm-up step)
     ms = timed(step, iters)
     res = {"train_step_ms": ms, "samples_per_gpu": samples, "global_batch": samples * world,
            "train_samples_s": samples * world / (ms * 1e-3),
@@ -405,8 +405,8 @@ def train_run(model, args, world, rank, dev, barrier, all_max, samples=32, iters
            "train_step": ("fwd + bwd + fused AdamW/EMA replayed as one CUDA graph" if cstep.captures > 0 else
                           "fwd + bwd + per-block NCCL all-reduce (AVG, fp32, overlapped) + fused AdamW/EMA, issued eagerly") + "; 3 x forward FLOPs counted"}
     if sync is not None:
-        with sync.no_sync():
-            ms_local = timed(step, iters)
+        with sync.no_sync():        # always the eager step: a captured graph has the collectives baked in
+            ms_local = timed(lambda: cstep._eager(x, t, y, pos, mask, tgt), iters)
         # the same buckets, all-reduced alone (nothing to overlap with)
         names = [n for n, _ in model.named_parameters()]
         sizes = {}

@@ -383,7 +383,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (RESID && leader) { issue_resid(0); issue_resid(1); }
 
     int q = 0;  // running slab index
-    int rope_m0 = -1;  // row block whose RoPE rows are in smemRope
+    int rope_m0 = -1;  // key of the row block whose RoPE rows are in smemRope (token offset for a shared table, else the row block itself)
     for (int it = 0; it < my_tiles; ++it) {
       const int tile = wid + it * nwork;
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
@@ -425,7 +425,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // the table rows of this tile's 128 tokens are staged in shared memory once per row block (column tiles of one row
           // block are consecutive): per-thread global reads of 288-byte-strided rows were the epilogue's critical path
           const int rs = p.rope_hd + 4;
-          if (m0 != rope_m0) {
+          // a table shared by all samples (rope_rows == 1) depends on the token index only: with 256-token samples every tile of this CTA
+          // holds the same 128 tokens, so the rows are staged once per kernel, not once per tile (37 KB from L2 each time)
+          const int rope_key = p.rope_rows == 1 && m0 + GT_BM <= p.M ? m0 % p.rope_tokens : -2 - m0;
+          if (rope_key != rope_m0) {
             const int q4 = p.rope_hd >> 2, total = QROWS * q4, et = half * 32 + lane;  // this quarter's 32 rows, by its 64 threads
             for (int i = et; i < total; i += 64) {
               const int rr = quarter * QROWS + i / q4, c4 = i - (i / q4) * q4;
@@ -433,7 +436,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const float4 v = __ldg(reinterpret_cast<const float4*>(p.rope_freqs + ((size_t)(p.rope_rows == 1 ? 0 : smp) * p.rope_tokens + tok) * p.rope_hd) + c4);
               *reinterpret_cast<float4*>(smemRope + rr * rs + c4 * 4) = v;
             }
-            rope_m0 = m0;  // visible to the quarter's threads after the first slab's named barrier
+            rope_m0 = rope_key;  // visible to the quarter's threads after the first slab's named barrier
           }
           rope_row = smemRope + row * rs;
         } else {
