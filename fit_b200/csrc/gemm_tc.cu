@@ -238,7 +238,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = wid; tile < num_tiles; tile += nwork, ++it) {
         const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
         // epilogue (of both CTAs of a pair) has drained this accumulator stage
-        if (PAIR) ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1); else ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+        // (plain wait also for the pair: the peer's arrivals order no memory -- the hand-off is "TMEM drained", fenced by tcgen05 -- and a
+        // cluster-scope acquire compiles to TRYWAIT + CCTL.IVALL, an L1 invalidate per tile under the epilogue's bias / gate / table reads)
+        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
         // tiles are 256 wide and only the last one of a row is cut to what is left (192- and 128-wide tiles measured 0.73x / 0.50x the
@@ -390,7 +392,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int m0 = (tile / tiles_n) * TM + row_off, n0 = (tile % tiles_n) * BN;
       const int m = min(m0 + row, p.M - 1);
       const float* gate_row = nullptr;
-      if (RESID) gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
+      if (RESID) {
+        gate_row = p.gate + (size_t)(m / p.rows_per_sample) * p.ld_gate;
+        // this tile's segment of the gate row -> L1 now, while the accumulator is still being formed: it changes with the sample (= with every
+        // tile at 256 tokens per sample), so each 16-byte read at its point of use below was a cold L2 round trip
+        if (half == 0 && lane < BN / 32 && n0 + lane * 32 < p.N) ptx::prefetch_l1(gate_row + n0 + lane * 32);
+      }
       float st1 = 0.f, st2 = 0.f;  // RESID: sum / sum of squares of this row's output columns handled by this thread (stats_out)
       // LNA: value = ln_a * acc + (ln_b * c1[s, n] + c2[s, n]) with ln_a = rstd, ln_b = -mean * rstd of this row of x
       float ln_a = 1.f, ln_b = 0.f;
