@@ -226,6 +226,7 @@ def ncu_traffic(tag="r1f"):
             gate_seen += 1
         elif name.startswith("attn_tc"): key = "attn_tc[softmax(qk^T)v]"
         elif name.startswith("ln_modulate"): key = "ln_modulate"
+        elif name.startswith("ln_apply"): key = "ln_apply"
         if key and key not in out:
             out[key] = b
     return out
@@ -299,14 +300,21 @@ def kernel_rooflines(model, sampler, peaks, iters=10):
             2.0 * M * D * 2 * Hp, (M * D + 2 * Hp * D + M * Hp) * 2)
         add("gemm_tc[qkv+rope]", lambda: ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS_ROPE, rope=sampler.pos, rope_cols=2 * D),
             2.0 * M * D * 3 * D, (M * D + 3 * D * D + M * 3 * D) * 2)
+    so = getattr(ws, "parts", None)   # the engine's GATE_RESID GEMMs also write the row sums of their output
     add("gemm_tc[fc2+gate+resid]", lambda: ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=W.n_mod,
-                                                     rows_per_sample=T, resid=ws.xs), 2.0 * M * Hp * D, (M * Hp + D * Hp) * 2 + 2 * M * D * bpe)
+                                                     rows_per_sample=T, resid=ws.xs, stats_out=so), 2.0 * M * Hp * D, (M * Hp + D * Hp) * 2 + 2 * M * D * bpe)
     add("gemm_tc[proj+gate+resid]", lambda: ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=W.n_mod,
-                                                      rows_per_sample=T, resid=ws.xs), 2.0 * M * D * D, (M * D + D * D) * 2 + 2 * M * D * bpe)
+                                                      rows_per_sample=T, resid=ws.xs, stats_out=so), 2.0 * M * D * D, (M * D + D * D) * 2 + 2 * M * D * bpe)
     add("attn_tc[softmax(qk^T)v]", lambda: ops.attention(ws.qkv, None, ws.kv_len, sampler.mask, 2 * sampler.B, T, h, dh, ws.att, prerotated=True),
         4.0 * (2 * sampler.B) * T * T * D, (M * 3 * D + M * D) * 2)
     if not fused:
-        add("ln_modulate", lambda: ops.ln_modulate(ws.xs, sh1, sc1, W.n_mod, T, ws.h), 0.0, M * D * (bpe + 2))
+        if getattr(ws, "parts", None) is not None:   # default bf16 path: row sums from the GATE_RESID epilogues, streaming modulate pass
+            from fit_b200.engine import LN_EPS
+            ops.row_stats(ws.xs, ws.parts)
+            add("ln_apply", lambda: ops.ln_apply(ws.xs, ws.parts, sh1, sc1, W.n_mod, T, ws.h, LN_EPS), 0.0, M * D * (bpe + 2) + ws.parts.numel() * 4)
+            add("row_stats", lambda: ops.row_stats(ws.xs, ws.parts), 0.0, M * D * bpe + ws.parts.numel() * 4)
+        else:
+            add("ln_modulate", lambda: ops.ln_modulate(ws.xs, sh1, sc1, W.n_mod, T, ws.h), 0.0, M * D * (bpe + 2))
     tb = sampler.diffusion._tables(sampler.device)
     nel = sampler.x.numel()
     add("cfg_ddpm_step", lambda: ops.cfg_step(sampler.x, sampler.raw, sampler.noise, sampler.t_idx[: sampler.B], tb["coef"], cfg_pairs=sampler.B,

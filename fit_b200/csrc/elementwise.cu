@@ -668,6 +668,43 @@ __global__ void __launch_bounds__(256) row_stats_kernel(const InT* __restrict__ 
   if (lane < nparts) parts[(size_t)row * nparts + lane] = lane == 0 ? make_float2(s1, s2) : make_float2(0.f, 0.f);
 }
 
+// modulate(LayerNorm(x)) for rows whose (sum, sum of squares) are already known -- fitb200_gemm_args.stats_out of the GATE_RESID GEMM that wrote
+// x, or row_stats: a pure streaming pass (16 bytes in, 16 bytes out per thread and step, no row held in registers, no reduction), 32 rows per CTA.
+constexpr int LNA_ROWS = 32;
+template <typename InT, typename OutT>
+__global__ void __launch_bounds__(256) ln_apply_kernel(const InT* __restrict__ x, int M, int D, int rows_per_sample, const float2* __restrict__ parts,
+                                                       int nparts, float eps, const float* __restrict__ shift, const float* __restrict__ scale,
+                                                       long ld_mod, OutT* __restrict__ out) {
+  __shared__ float2 st[LNA_ROWS];   // (rstd, -mean * rstd)
+  // rows are walked from the END of the tensor (see ln_modulate_kernel): the producer GEMM wrote its last rows most recently
+  const int row0 = (gridDim.x - 1 - blockIdx.x) * LNA_ROWS;
+  if (threadIdx.x < LNA_ROWS) {
+    const int row = row0 + threadIdx.x;
+    if (row < M) {
+      float s1 = 0.f, s2 = 0.f;
+      for (int i = 0; i < nparts; ++i) { const float2 t = __ldg(parts + (size_t)row * nparts + i); s1 += t.x; s2 += t.y; }
+      const float mu = s1 / (float)D;
+      const float rstd = 1.0f / sqrtf(fmaxf(s2 / (float)D - mu * mu, 0.f) + eps);
+      st[threadIdx.x] = make_float2(rstd, -mu * rstd);
+    }
+  }
+  __syncthreads();
+  const int nvec = D >> 3;
+  const int total = min(LNA_ROWS, M - row0) * nvec;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int rl = i / nvec, c = i - rl * nvec;
+    const int row = row0 + rl;
+    const size_t mrow = (size_t)(row / rows_per_sample) * ld_mod + c * 8;
+    Vec8<InT> v = Vec8<InT>::load(x + (size_t)row * D + c * 8);
+    const Vec8<float> sc = Vec8<float>::load(scale + mrow), sh = Vec8<float>::load(shift + mrow);
+    const float2 ab = st[rl];
+    Vec8<OutT> o;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o.v[e] = fmaf(fmaf(v.v[e], ab.x, ab.y), 1.0f + sc.v[e], sh.v[e]);
+    o.store(out + (size_t)row * D + c * 8);
+  }
+}
+
 // out[set][s][k] = bf16(1 + scale_set[s,k]),  out[set][S + s][k] = bf16(shift_set[s,k])
 __global__ void __launch_bounds__(256) modulation_pack_kernel(const float* __restrict__ shift, const float* __restrict__ scale, long ld_mod, int S, int D,
                                                            int n_sets, long set_stride, __nv_bfloat16* __restrict__ out) {
@@ -892,6 +929,22 @@ int fitb200_modulation_pack(const float* shift, const float* scale, int64_t ld_m
   const long total = (long)n_sets * 2 * S * (D / 4);
   modulation_pack_kernel<<<step_grid(total), 256, 0, (cudaStream_t)stream>>>(shift, scale, ld_mod, S, D, n_sets, set_stride, (__nv_bfloat16*)out);
   FITB200_CHECK_LAUNCH("modulation_pack");
+  return FITB200_OK;
+}
+
+int fitb200_ln_apply_fwd(const void* x, int x_dtype, int M, int D, int rows_per_sample, const float* parts, int nparts, float eps,
+                         const float* shift, const float* scale, int64_t ld_mod, void* out, int out_dtype, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && parts && shift && scale && out && M > 0 && rows_per_sample > 0 && nparts >= 1, "ln_apply: bad arguments");
+  FITB200_CHECK_ARG(D % 8 == 0 && ld_mod % 4 == 0 && ((uintptr_t)shift & 15) == 0 && ((uintptr_t)scale & 15) == 0 && ((uintptr_t)parts & 7) == 0,
+                    "ln_apply: D=%d must be a multiple of 8, shift / scale 16-byte aligned", D);
+  const unsigned grid = (unsigned)ceil_div(M, LNA_ROWS);
+  FITB200_DISPATCH_ACT(x_dtype, InT, {
+    FITB200_DISPATCH_ACT(out_dtype, OutT, {
+      ln_apply_kernel<InT, OutT><<<grid, 256, 0, (cudaStream_t)stream>>>((const InT*)x, M, D, rows_per_sample, (const float2*)parts, nparts, eps, shift,
+                                                                        scale, ld_mod, (OutT*)out);
+    })
+  })
+  FITB200_CHECK_LAUNCH("ln_apply");
   return FITB200_OK;
 }
 

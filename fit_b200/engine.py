@@ -108,6 +108,12 @@ def ln_prologue_ok(precision: str, M: int, D: int, T: int) -> bool:
     return precision == "bf16" and M > 128 and T % 128 == 0 and D > 128 and D % 64 == 0 and os.environ.get("FITB200_LN_FUSE", "0") == "1"
 
 
+def ln_stats_ok(precision: str, D: int) -> bool:
+    """bf16 path: the proj / fc2 GEMM epilogues emit the row sums of the residual stream they write (stats_out), so modulate(norm(x)) is a
+    streaming pass (ln_apply) instead of a row-reduction kernel.  FITB200_LN_STATS=0 keeps ln_modulate (A/B)."""
+    return precision == "bf16" and D % 8 == 0 and os.environ.get("FITB200_LN_STATS", "1") != "0"
+
+
 class _Workspace:
     def __init__(self, R: int, T: int, D: int, Hp: int, n_mod: int, act: torch.dtype, device):
         M = R * T
@@ -121,7 +127,9 @@ class _Workspace:
             self.modA = torch.empty(2 * L6, 2 * R, D, dtype=torch.bfloat16, **z)
             self.cq = torch.empty(2 * R, 3 * D, dtype=torch.float32, **z)
             self.cf = torch.empty(2 * R, 2 * Hp, dtype=torch.float32, **z)
-            self.parts = torch.empty(M, ops.gemm_stats_parts(D), 2, dtype=torch.float32, **z)
+        self.parts = None
+        if self.modA is not None or ln_stats_ok("bf16" if act == torch.bfloat16 else "fp32", D):
+            self.parts = torch.empty(M, ops.gemm_stats_parts(D), 2, dtype=torch.float32, **z)   # partial row sums of the residual stream
         self.xs = torch.empty(M, D, dtype=act, **z)
         self.h = torch.empty(M, D, dtype=act, **z)
         self.qkv = torch.empty(M, 3 * D, dtype=act, **z)
@@ -212,7 +220,11 @@ class FiTEngine:
             ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=nm, rows_per_sample=T, resid=ws.xs,
                      stats_out=ws.parts)
             return
-        ops.ln_modulate(ws.xs, sh1, sc1, nm, T, ws.h)
+        parts = getattr(ws, "parts", None)   # row sums of ws.xs (from row_stats / the previous GATE_RESID epilogue): LN without the row reduction
+        if parts is not None:
+            ops.ln_apply(ws.xs, parts, sh1, sc1, nm, T, ws.h, LN_EPS)
+        else:
+            ops.ln_modulate(ws.xs, sh1, sc1, nm, T, ws.h)
         if self.precision == "bf16":
             # apply_rotary_emb (fit.py:160-174) rides in the qkv GEMM epilogue (fp32 accumulators, q and k columns), so the
             # attention kernel fetches finished operands with TMA
@@ -221,13 +233,16 @@ class FiTEngine:
         else:
             ops.gemm(ws.h, e["qkv_w"], e["qkv_b"], ws.qkv, EPI_BIAS)
             ops.attention(ws.qkv, pos, ws.kv_len, mask, R, T, m.num_heads, D // m.num_heads, ws.att)
-        ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=nm, rows_per_sample=T, resid=ws.xs)
-        ops.ln_modulate(ws.xs, sh2, sc2, nm, T, ws.h)
+        ops.gemm(ws.att, e["proj_w"], e["proj_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g1, ld_gate=nm, rows_per_sample=T, resid=ws.xs, stats_out=parts)
+        if parts is not None:
+            ops.ln_apply(ws.xs, parts, sh2, sc2, nm, T, ws.h, LN_EPS)
+        else:
+            ops.ln_modulate(ws.xs, sh2, sc2, nm, T, ws.h)
         if self.precision == "bf16":
             ops.gemm(ws.h, e["fc1_w"], e["fc1_b"], ws.g, EPI_SWIGLU)
         else:
             ops.gemm(ws.h, e["fc1_g_w"], e["fc1_g_b"], ws.g, EPI_SWIGLU, B2=e["fc1_x_w"], bias2=e["fc1_x_b"])
-        ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=nm, rows_per_sample=T, resid=ws.xs)
+        ops.gemm(ws.g, e["fc2_w"], e["fc2_b"], ws.xs, EPI_BIAS_GATE_RESID, gate=g2, ld_gate=nm, rows_per_sample=T, resid=ws.xs, stats_out=parts)
 
     # ------------------------------------------------------------------ sub-module entry points (fit.py:229-250,277-285,326-337; dit.py:138-142)
     class _Scratch:
@@ -370,7 +385,7 @@ class FiTEngine:
             ops.mask_to_kvlen(mask, ws.kv_len, ws.n_valid)
             ops.embed_tokens(x, W.x_w, W.x_b, ws.xs, R, T, p, C_in)
             self.conditioning(ws, W, t, y)
-            if ws.modA is not None:
+            if ws.parts is not None:
                 ops.row_stats(ws.xs, ws.parts)
         if collect is not None:
             collect.append(ws.xs.float().view(R, T, D).clone())

@@ -149,6 +149,16 @@ def ln_modulate(x: Tensor, shift: Tensor, scale: Tensor, ld_mod: int, rows_per_s
     return out
 
 
+def ln_apply(x: Tensor, parts: Tensor, shift: Tensor, scale: Tensor, ld_mod: int, rows_per_sample: int, out: Tensor, eps: float = 1e-6):
+    """ln_modulate for rows whose partial (sum, sum of squares) are in ``parts`` [M, nparts, 2] (gemm(..., stats_out=parts) / row_stats)."""
+    L.require_cuda(x, parts, shift, scale, out)
+    M, D = x.shape
+    assert parts.dtype == torch.float32 and parts.is_contiguous() and parts.shape[0] == M and parts.shape[2] == 2
+    L.check(L.lib().fitb200_ln_apply_fwd(L.ptr(_c(x)), L.dtype_code(x), M, D, rows_per_sample, L.ptr(parts), parts.shape[1], eps, L.ptr(shift),
+                                         L.ptr(scale), ld_mod, L.ptr(out), L.dtype_code(out), L.stream_ptr()), "ln_apply")
+    return out
+
+
 def attention(qkv: Tensor, freqs: Optional[Tensor], kv_len: Tensor, mask: Optional[Tensor], R: int, T: int, h: int, d: int,
               out: Tensor, lse: Optional[Tensor] = None, prerotated: bool = False):
     """qkv [R*T, 3*h*d] -> out [R*T, h*d]; RoPE + key-masked softmax attention.

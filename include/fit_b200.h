@@ -171,6 +171,11 @@ int fitb200_attn_bwd(const void* qkv, int dtype, const float* freqs, int freqs_r
                      int R, int T, int h, int d, int flags, const void* out, const void* dout, const float* lse, void* dqkv,
                      fitb200_stream_t stream);
 
+/* The same for rows whose partial (sum x, sum x^2) are already known -- written by the GATE_RESID GEMM that produced x (fitb200_gemm_args.stats_out)
+ * or by fitb200_row_stats: a streaming pass without the row reduction.  parts: fp32 [M, nparts, 2]; eps: the LayerNorm epsilon (1e-6). */
+int fitb200_ln_apply_fwd(const void* x, int x_dtype, int M, int D, int rows_per_sample, const float* parts, int nparts, float eps,
+                         const float* shift, const float* scale, int64_t ld_mod, void* out, int out_dtype, fitb200_stream_t stream);
+
 /* ---- final layer ---------------------------------------------------------------------------------
  * FinalLayer.forward (dit.py:138-142) after its adaLN Linear: LN + modulate + Linear(D -> P) with
  * P = p*p*C_out, optionally fused with FiT.unpatchify (fit.py:444-456).

@@ -359,3 +359,23 @@ def test_attention_kv_blocked_long(ops, T, h, d, nonprefix):
         q0 = (L + 127) // 128 * 128
         if q0 < T:
             assert float(out[r, q0:].abs().max()) == 0.0   # query tiles beyond kv_len are zero rows
+
+
+@pytest.mark.parametrize("xdt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,D,rps", [(512, 1152, 256), (77, 144, 20), (4100, 768, 200)])
+def test_ln_apply_from_row_sums(ops, xdt, M, D, rps):
+    """modulate(LayerNorm(x)) from known row sums (row_stats here; the GATE_RESID GEMM epilogue in the engine) == the row-reduction kernel."""
+    g = torch.Generator().manual_seed(M + D)
+    S = (M + rps - 1) // rps
+    x = (torch.randn(M, D, generator=g) * 1.5 + 0.3).to(xdt)
+    mod = torch.randn(S, 2 * D, generator=g) * 0.4
+    xd = x.double()
+    h = F.layer_norm(xd, (D,), eps=1e-6)
+    want = h * (1 + mod[:, D:].double().repeat_interleave(rps, 0)[:M]) + mod[:, :D].double().repeat_interleave(rps, 0)[:M]
+    modc = mod.cuda()
+    parts = torch.full((M, 3, 2), float("nan"), device="cuda")
+    ops.row_stats(x.cuda(), parts)
+    for odt in (torch.float32, torch.bfloat16):
+        out = torch.empty(M, D, dtype=odt, device="cuda")
+        ops.ln_apply(x.cuda(), parts, modc[:, :D], modc[:, D:], 2 * D, rps, out)
+        assert rel_l2(out.float(), want) < (1e-5 if odt == torch.float32 else 4e-3)
