@@ -10,7 +10,7 @@ ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control no
 echo "launch-list exit $?"; tail -1 gpurun_out/step_plain_$TAG.log
 python tools/step_share.py gpurun_out/launches_$TAG.csv > gpurun_out/${TAG}_step_share.txt; head -14 gpurun_out/${TAG}_step_share.txt
 python tools/prof_kernels.py > gpurun_out/prof_plain_$TAG.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:"${PROF_REGEX:-gemm_tc|attn_|ln_modulate}" -s ${PROF_SKIP:-9} -c ${PROF_COUNT:-9} -f -o gpurun_out/prof_$TAG \
+ncu --set full --clock-control none --import-source on -k regex:"${PROF_REGEX:-gemm_tc|attn_|ln_modulate|ln_apply}" -s ${PROF_SKIP:-9} -c ${PROF_COUNT:-9} -f -o gpurun_out/prof_$TAG \
     python tools/prof_kernels.py > gpurun_out/prof_ncu_$TAG.log 2>&1
 echo "ncu exit $?"; tail -3 gpurun_out/prof_ncu_$TAG.log
 python tools/ncu_summary.py gpurun_out/prof_$TAG.ncu-rep gpurun_out/${TAG}_ncu_full_block_kernels.csv > /dev/null 2>&1; echo "summary exit $?"
