@@ -1,6 +1,6 @@
 // fp32 CUDA-core attention for the verification mode: thread-per-query online softmax with the 2-D
 // RoPE applied while q / k are loaded, key masking from kv_len + mask bytes.
-// (The bf16 production kernel lives in attn_mma.cu; both share the entry point fitb200_attn_fwd.)
+// (The bf16 kernels are attn_tc2.cu / attn_tc3.cu; the shared entry point fitb200_attn_fwd is in attn_dispatch.cu.)
 #include "common.cuh"
 
 namespace fitb200 {

@@ -153,9 +153,10 @@ int fitb200_ln_modulate_fwd(const void* x, int x_dtype, int M, int D, int rows_p
  * padding whose reference output is unspecified).  out: [R, T, h*d].
  * lse: optional fp32 [R, h, T] log-sum-exp (natural log, of the scaled scores) for backward.
  * d in {64, 72}.
- * flags: FITB200_ATTN_PREROTATED = q and k in qkv already carry the RoPE (written by a FITB200_EPI_BIAS_ROPE GEMM);
- *        freqs is then ignored (may be NULL).  bf16 only.
- * bf16, T <= 256: tcgen05 / TMEM kernel (attn_tc.cu); bf16, T > 256: chunked mma.sync kernel; fp32: CUDA-core kernel. */
+ * flags: FITB200_ATTN_PREROTATED = q and k in qkv already carry the RoPE (written by a FITB200_EPI_BIAS_ROPE GEMM); freqs is then ignored
+ *        (may be NULL).  REQUIRED for bf16 (un-rotated bf16 operands return FITB200_ERR_UNSUPPORTED); not accepted for fp32.
+ * bf16, T <= 256: persistent tcgen05 / TMEM kernel (attn_tc2.cu); bf16, T > 256: KV-blocked tcgen05 kernel (attn_tc3.cu); fp32: CUDA-core
+ * kernel with the RoPE applied in the kernel (attn_simt.cu). */
 enum { FITB200_ATTN_PREROTATED = 1, FITB200_ATTN_FORCE_SIMT = 2 /* backward only: take the CUDA-core kernel */ };
 int fitb200_attn_fwd(const void* qkv, int dtype, const float* freqs, int freqs_rows, const int32_t* kv_len,
                      const uint8_t* mask, int R, int T, int h, int d, int flags, void* out, float* lse,
