@@ -24,6 +24,10 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr", "-DFITB200_BUILD",
 ]
+if os.environ.get("FITB200_NVCC_EXTRA"):       # A/B builds of one tuning macro (python -m fit_b200.build with FITB200_LIB_OUT=<other .so>)
+    NVCC_FLAGS += os.environ["FITB200_NVCC_EXTRA"].split()
+    LIB = os.environ.get("FITB200_LIB_OUT", LIB)
+    OBJDIR = OBJDIR + "_alt"
 if os.environ.get("FITB200_TUNING") == "1":   # measurement-only switches (e.g. FITB200_GEMM_DBG: GEMM mainloop ceiling); never in the product build
     NVCC_FLAGS.append("-DFITB200_TUNING")
 

@@ -31,7 +31,10 @@ constexpr int GT_THREADS_LNA = 512;
 constexpr int GT_LNA_ROWS = 128 / (GT_LNA_THREADS / 8);   // rows per rescaler thread
 constexpr int GT_BAR_BYTES = 512;
 constexpr int GT_SLAB_BYTES = GT_BM * 128;  // 128 rows x 128 bytes
-constexpr int GT_ROPE_MAX_HD = 72;          // head dims up to this keep the tile's RoPE rows in shared memory (FiT: 64, 72)
+#ifndef FITB200_ROPE_SMEM_HD
+#define FITB200_ROPE_SMEM_HD 72
+#endif
+constexpr int GT_ROPE_MAX_HD = FITB200_ROPE_SMEM_HD;  // head dims up to this keep the tile's RoPE rows in shared memory (FiT: 64, 72)
 constexpr int GT_SMEM_BUDGET = 232448 - 1024 /*align slack*/ - GT_BAR_BYTES /*barriers*/;
 
 // PAIR: two CTAs of a cluster (one TPC) share one 256 x BN tile through tcgen05 cta_group::2 -- each CTA stages its own 128 rows of A
@@ -48,7 +51,12 @@ template <int BN, int EPI, bool PAIR = false, bool LNA = false> struct GtCfg {
   static constexpr int LNC_BYTES = LNA ? 4 * 2 * BN * 4 : 0;
   static constexpr int EPI_BYTES = (EPI == FITB200_EPI_BIAS_GATE_RESID ? 4 : 2) * GT_SLAB_BYTES + ROPE_BYTES + LNC_BYTES;
   static constexpr int STAGES_RAW = (GT_SMEM_BUDGET - EPI_BYTES) / STAGE_BYTES;
-  static constexpr int STAGES = STAGES_RAW > (PAIR ? 8 : 6) ? (PAIR ? 8 : 6) : STAGES_RAW;
+#ifdef FITB200_MAX_STAGES   // tuning builds: cap the ring depth (how much of a kernel's rate is its stage count?)
+  static constexpr int STAGES_CAP = FITB200_MAX_STAGES;
+#else
+  static constexpr int STAGES_CAP = PAIR ? 8 : 6;
+#endif
+  static constexpr int STAGES = STAGES_RAW > STAGES_CAP ? STAGES_CAP : STAGES_RAW;
   static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;  // 2 accumulator stages, power of two
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + GT_BAR_BYTES;
   static_assert(STAGES >= 3, "pipeline too shallow");
@@ -378,6 +386,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // residual slab q (running index over this CTA's tiles) -> TMA load into resid buffer q & 1
     auto issue_resid = [&](int qq) {
       if (qq >= total_slabs) return;
+#ifdef FITB200_TUNING
+      if (p.dbg & 4) return;
+#endif
       const int tile = wid + (qq / NSLAB) * nwork, slab = qq % NSLAB;
       const int rm0 = (tile / tiles_n) * TM + row_off, rn0 = (tile % tiles_n) * BN + slab * OUTC;
       ptx::mbar_arrive_expect_tx(&res_bar[quarter * 2 + (qq & 1)], QBYTES);
@@ -460,7 +471,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
 #ifdef FITB200_TUNING  // measurement-only builds (FITB200_TUNING=1 python -m fit_b200.build): mainloop ceiling with the epilogue skipped
-      if (p.dbg) {
+      if (p.dbg == 1) {
         ptx::tc_fence_before();
         if (PAIR) { __syncwarp(); if (lane == 0) ptx::mbar_arrive_cluster_relaxed(tempty_leader + as * 8); } else ptx::mbar_arrive(&tempty_bar[as]);
         q += NSLAB;
@@ -484,7 +495,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         // the TMA store that read this staging buffer two slabs ago must have finished reading it
         if (leader) ptx::tma_store_wait_read<1>();
+#ifdef FITB200_TUNING
+        if (RESID && !(p.dbg & 4)) ptx::mbar_wait(&res_bar[quarter * 2 + buf], (q >> 1) & 1);
+#else
         if (RESID) ptx::mbar_wait(&res_bar[quarter * 2 + buf], (q >> 1) & 1);
+#endif
         ptx::named_bar_sync(qbar, 64);
         if (live) {
           float acc[HACC];
@@ -578,11 +593,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int i4 = 0; i4 < CW / 4; ++i4) {
                   float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#ifdef FITB200_TUNING
+                  if (ok && !(p.dbg & 8)) g4 = __ldg(reinterpret_cast<const float4*>(gate_row + nb + i4 * 4));
+#else
                   if (ok) g4 = __ldg(reinterpret_cast<const float4*>(gate_row + nb + i4 * 4));
+#endif
                   v[i4 * 4 + 0] = fmaf(g4.x, v[i4 * 4 + 0], r[i4 * 4 + 0]); v[i4 * 4 + 1] = fmaf(g4.y, v[i4 * 4 + 1], r[i4 * 4 + 1]);
                   v[i4 * 4 + 2] = fmaf(g4.z, v[i4 * 4 + 2], r[i4 * 4 + 2]); v[i4 * 4 + 3] = fmaf(g4.w, v[i4 * 4 + 3], r[i4 * 4 + 3]);
                 }
+#ifdef FITB200_TUNING
+                if (ok && !(p.dbg & 2)) {
+#else
                 if (ok) {  // row statistics of the new residual stream: the LayerNorm that follows never re-reads x for them
+#endif
 #pragma unroll
                   for (int i = 0; i < CW; ++i) { st1 += v[i]; st2 = fmaf(v[i], v[i], st2); }
                 }
