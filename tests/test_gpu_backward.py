@@ -7,7 +7,7 @@ import pytest
 import torch
 import torch.nn.functional as F
 
-from helpers import TINY64, TINY72, TINY_SHAPES, build_model, golden, rel_l2
+from helpers import TINY64, TINY72, TINY_SHAPES, build_model, golden, record, rel_l2
 
 pytestmark = pytest.mark.gpu
 
@@ -208,7 +208,8 @@ def _grad_check(z, model, sampled, tol):
 
 
 @pytest.mark.parametrize("name,cfg", [("fit_tiny_d64", TINY64), ("fit_tiny_d72", TINY72)])
-@pytest.mark.parametrize("precision,tol_loss,tol_grad", [("fp32", 1e-5, 1e-3), ("bf16", 2e-2, 6e-2)])
+# measured on B200 (profiles/*_parity_measured.txt): fp32 worst gradient 7.5e-7, bf16 8.1e-3 (loss 4e-5)
+@pytest.mark.parametrize("precision,tol_loss,tol_grad", [("fp32", 1e-5, 2e-5), ("bf16", 1e-3, 2e-2)])
 def test_tiny_training_step_matches_reference(name, cfg, precision, tol_loss, tol_grad):
     """loss.backward() through the custom autograd node vs the reference's autograd (goldens from the unmodified reference)."""
     from fit_b200.train import masked_mse_loss
@@ -226,10 +227,12 @@ def test_tiny_training_step_matches_reference(name, cfg, precision, tol_loss, to
     loss.backward()
     assert abs(float(loss) - float(z["loss"])) < tol_loss * abs(float(z["loss"]))
     worst = _grad_check(z, model, sampled=False, tol=tol_grad)
+    record(f"tiny_train_step {name} [{precision}] loss_rel / worst grad rel-L2", f"{abs(float(loss) - float(z['loss'])) / abs(float(z['loss'])):.3e} / {worst[1]:.3e} ({worst[0]})")
     assert worst[1] < tol_grad, worst
 
 
-@pytest.mark.parametrize("precision,tol_loss,tol_grad", [("fp32", 1e-5, 2e-3), ("bf16", 2e-2, 8e-2)])
+# measured on B200: fp32 worst gradient 6.5e-6, bf16 1.5e-2 (12 blocks; loss 2e-5)
+@pytest.mark.parametrize("precision,tol_loss,tol_grad", [("fp32", 1e-5, 1e-4), ("bf16", 1e-3, 3e-2)])
 def test_b2_mixed_resolution_training_step(precision, tol_loss, tol_grad):
     """BASELINE config 2: FiT-B/2, mixed-resolution batch (256^2, 160x320, 128x512 padded to 256 tokens + mask), forward + backward."""
     from fit_b200.train import masked_mse_loss
@@ -247,4 +250,5 @@ def test_b2_mixed_resolution_training_step(precision, tol_loss, tol_grad):
     assert abs(float(loss) - float(z["loss"])) < tol_loss * abs(float(z["loss"]))
     full = z["g.x_embedder.bias"].size == cfg["hidden_size"] and z["g.blocks.0.attn.qkv.weight"].size == 3 * cfg["hidden_size"] ** 2
     worst = _grad_check(z, model, sampled=not full, tol=tol_grad)
+    record(f"b2_mixed_train_step [{precision}] loss_rel / worst grad rel-L2", f"{abs(float(loss) - float(z['loss'])) / abs(float(z['loss'])):.3e} / {worst[1]:.3e} ({worst[0]})")
     assert worst[1] < tol_grad, worst
