@@ -705,6 +705,17 @@ __global__ void __launch_bounds__(256) ln_apply_kernel(const InT* __restrict__ x
   }
 }
 
+// FiT.unpatchify (fit.py:444-456) as an index map: tokens [R, T, P = p*p*C] -> latents [R, C, H, W] (the tensor-core final layer writes tokens)
+__global__ void __launch_bounds__(256) unpatchify_kernel(const float* __restrict__ tok, int R, int T, int C, int H, int W, int p, float* __restrict__ out) {
+  const long n = (long)R * C * H * W;
+  const int nw = W / p, P = p * p * C;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W), y = (int)((i / W) % H), c = (int)((i / ((long)W * H)) % C), r = (int)(i / ((long)W * H * C));
+    const int tk = (y / p) * nw + x / p, pp = (y % p) * p + x % p;
+    out[i] = tok[((size_t)r * T + tk) * P + pp * C + c];
+  }
+}
+
 // out[set][s][k] = bf16(1 + scale_set[s,k]),  out[set][S + s][k] = bf16(shift_set[s,k])
 __global__ void __launch_bounds__(256) modulation_pack_kernel(const float* __restrict__ shift, const float* __restrict__ scale, long ld_mod, int S, int D,
                                                            int n_sets, long set_stride, __nv_bfloat16* __restrict__ out) {
@@ -945,6 +956,13 @@ int fitb200_ln_apply_fwd(const void* x, int x_dtype, int M, int D, int rows_per_
     })
   })
   FITB200_CHECK_LAUNCH("ln_apply");
+  return FITB200_OK;
+}
+
+int fitb200_unpatchify(const float* tokens, int R, int T, int C, int H, int W, int p, float* out, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(tokens && out && R > 0 && C > 0 && p > 0 && H % p == 0 && W % p == 0 && (H / p) * (W / p) == T, "unpatchify: inconsistent shape");
+  unpatchify_kernel<<<step_grid((long)R * C * H * W), 256, 0, (cudaStream_t)stream>>>(tokens, R, T, C, H, W, p, out);
+  FITB200_CHECK_LAUNCH("unpatchify");
   return FITB200_OK;
 }
 

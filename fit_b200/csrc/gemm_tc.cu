@@ -119,7 +119,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int NSLAB = BN / ACCC;
   constexpr int CW = 16 / (int)sizeof(OutT);          // output columns per 16-byte chunk: 8 (bf16) or 4 (fp32)
   static_assert(BN % ACCC == 0, "tile width must be a whole number of slabs");
-  static_assert(!LNA || (PAIR && !AMN && !BMN && sizeof(OutT) == 2 && (ROPE || SWIGLU || EPI == FITB200_EPI_BIAS)), "LNA: K-major pair tiles, bf16 output");
+  static_assert(!LNA || (PAIR && !AMN && !BMN && (ROPE || SWIGLU || EPI == FITB200_EPI_BIAS) && (sizeof(OutT) == 2 || EPI == FITB200_EPI_BIAS)),
+                "LNA: K-major pair tiles; bf16 output (fp32 with the plain BIAS epilogue: the final layer)");
   constexpr int LNA_WARPS = GT_LNA_THREADS / 32;
   constexpr int EPI_WARP0 = LNA ? 4 : 2;          // first epilogue warp (a multiple of 4 apart from the TMEM lane quarter rule: quarter = warp % 4)
 
@@ -780,17 +781,17 @@ static int dispatch_epi(const fitb200_gemm_args& a, cudaStream_t s) {
   }
   // K-major operands: CTA pairs (256 x BN tiles, cta_group::2) whenever there are at least two row blocks; FITB200_GEMM_PAIR=0 forces single-CTA tiles
   static const bool pair_ok = [] { const char* e = getenv("FITB200_GEMM_PAIR"); return !(e && e[0] == '0'); }();
-  if (a.ln_g) {  // LayerNorm + modulate prologue: 256-wide pair tiles, bf16 output
-    if constexpr (BN == 256 && sizeof(OutT) == 2) {
+  if (a.ln_g) {  // LayerNorm + modulate prologue: 256-wide pair tiles (any N: a narrow output is one cut tile per row block)
+    if constexpr (BN == 256) {
       if (a.M > GT_BM) {
-        switch (a.epilogue) {
-          case FITB200_EPI_BIAS: return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, false, true, true>(a, s);
-          case FITB200_EPI_BIAS_ROPE: return launch_tc<BN, FITB200_EPI_BIAS_ROPE, OutT, false, false, true, true>(a, s);
-          case FITB200_EPI_SWIGLU: return launch_tc<BN, FITB200_EPI_SWIGLU, OutT, false, false, true, true>(a, s);
+        if (a.epilogue == FITB200_EPI_BIAS) return launch_tc<BN, FITB200_EPI_BIAS, OutT, false, false, true, true>(a, s);
+        if constexpr (sizeof(OutT) == 2) {
+          if (a.epilogue == FITB200_EPI_BIAS_ROPE) return launch_tc<BN, FITB200_EPI_BIAS_ROPE, OutT, false, false, true, true>(a, s);
+          if (a.epilogue == FITB200_EPI_SWIGLU) return launch_tc<BN, FITB200_EPI_SWIGLU, OutT, false, false, true, true>(a, s);
         }
       }
     }
-    set_last_error("gemm_bf16_tc: the LN prologue needs M > 128, N > 128, bf16 output and a BIAS / BIAS_ROPE / SWIGLU epilogue");
+    set_last_error("gemm_bf16_tc: the LN prologue needs M > 128 and a BIAS (bf16 / fp32 output) or BIAS_ROPE / SWIGLU (bf16 output) epilogue");
     return FITB200_ERR_UNSUPPORTED;
   }
   if (pair_ok && a.M > GT_BM) {
@@ -824,7 +825,7 @@ static int dispatch_bn(const fitb200_gemm_args& a, cudaStream_t s) {
   static const int force = [] { const char* e = getenv("FITB200_GEMM_BN"); return e ? atoi(e) : 0; }();
   // (tried: 128-wide tiles when they need fewer wave x width units at training sizes -- 47.4 vs 42.5 ms per XL/2 step: N = 128 tiles are
   // shared-memory-bandwidth bound, so 256 stays)
-  const int best = force ? force : (a.N <= 128 ? 128 : 256);
+  const int best = a.ln_g ? 256 : force ? force : (a.N <= 128 ? 128 : 256);
   if (best == 256) return dispatch_epi<256, OutT>(a, s);
   if (best == 192) return dispatch_epi<192, OutT>(a, s);
   return dispatch_epi<128, OutT>(a, s);

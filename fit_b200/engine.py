@@ -93,6 +93,7 @@ class _Weights:
             e["fc2_b"] = f32(blk.ffn.fc2.bias)
             self.blocks.append(e)
         self.fin_w, self.fin_b = f32(model.final_layer.linear.weight), f32(model.final_layer.linear.bias)
+        self.fin_w16 = w(model.final_layer.linear.weight) if bf16 else None   # tensor-core final layer (GEMM with the LayerNorm prologue)
 
 
 LN_EPS = 1e-6  # norm1 / norm2 (fit.py:303,308)
@@ -106,6 +107,14 @@ def ln_prologue_ok(precision: str, M: int, D: int, T: int) -> bool:
     Shapes served: bf16, every 128-row CTA tile inside one sample (T % 128 == 0: the reference's 256-token sequences and the 1024 / 4096-token
     extrapolation shapes), width a whole number of 64-column k-slabs (every FiT size: 384, 768, 1024, 1152)."""
     return precision == "bf16" and M > 128 and T % 128 == 0 and D > 128 and D % 64 == 0 and os.environ.get("FITB200_LN_FUSE", "0") == "1"
+
+
+def final_gemm_ok(precision: str, M: int, D: int, T: int) -> bool:
+    """The final layer (LayerNorm + modulate + Linear(D -> p*p*C), dit.py:138-142) as ONE tcgen05 GEMM with the LayerNorm prologue: with 16
+    output columns the GEMM is a single pass over the residual stream, so here the prologue is a clear gain (0.1 ms against 0.6 ms for the
+    CUDA-core kernel, which issues 576 fp32 FMAs per token and lane).  Same shape conditions as the prologue; FITB200_FINAL_GEMM=0 keeps the
+    CUDA-core kernel (the fp32 verification mode and every other shape take it anyway)."""
+    return precision == "bf16" and M > 128 and T % 128 == 0 and D > 128 and D % 64 == 0 and os.environ.get("FITB200_FINAL_GEMM", "1") != "0"
 
 
 def ln_stats_ok(precision: str, D: int) -> bool:
@@ -130,6 +139,12 @@ class _Workspace:
         self.parts = None
         if self.modA is not None or ln_stats_ok("bf16" if act == torch.bfloat16 else "fp32", D):
             self.parts = torch.empty(M, ops.gemm_stats_parts(D), 2, dtype=torch.float32, **z)   # partial row sums of the residual stream
+        # final layer as a GEMM with the LayerNorm + modulate PROLOGUE (dit.py:138-142): packed modulation rows, (c1, c2) vectors, token output
+        self.fin_mod = None
+        if final_gemm_ok("bf16" if act == torch.bfloat16 else "fp32", M, D, T) and self.parts is not None:
+            self.fin_mod = torch.empty(1, 2 * R, D, dtype=torch.bfloat16, **z)
+            self.fin_c = None      # [2R, P] fp32, allocated at first use (P is the caller's)
+            self.fin_tok = None    # [M, P] fp32
         self.xs = torch.empty(M, D, dtype=act, **z)
         self.h = torch.empty(M, D, dtype=act, **z)
         self.qkv = torch.empty(M, 3 * D, dtype=act, **z)
@@ -399,5 +414,17 @@ class FiTEngine:
             out = torch.empty((R, T, P) if train else (R, m.out_channels, H, Wd), dtype=torch.float32, device=x.device)
         sh, sc = ws.fin_views
         with rng("fit/final_layer"):
-            ops.final_layer(ws.xs, sh, sc, W.n_mod, W.fin_w, W.fin_b, out, R, T, p, m.out_channels)
+            if getattr(ws, "fin_mod", None) is not None and W.fin_w16 is not None and P % 8 == 0:
+                if ws.fin_c is None or ws.fin_c.shape[1] != P:
+                    ws.fin_c = torch.empty(2 * R, P, dtype=torch.float32, device=x.device)
+                    ws.fin_tok = torch.empty(R * T, P, dtype=torch.float32, device=x.device)
+                # row sums of ws.xs: written by the last block's fc2 epilogue (or row_stats when the network has no blocks)
+                ops.modulation_pack(sh, sc, W.n_mod, R, D, 1, 0, ws.fin_mod)
+                ops.gemm(ws.fin_mod[0], W.fin_w16, W.fin_b, ws.fin_c, EPI_BIAS, bias_row0=R)
+                tok = out.view(R * T, P) if train else ws.fin_tok
+                ops.gemm(ws.xs, W.fin_w16, None, tok, EPI_BIAS, rows_per_sample=T, ln=(ws.fin_mod[0, :R], ws.fin_c, ws.parts, LN_EPS))
+                if not train:
+                    ops.unpatchify(ws.fin_tok.view(R, T, P), out, p)
+            else:
+                ops.final_layer(ws.xs, sh, sc, W.n_mod, W.fin_w, W.fin_b, out, R, T, p, m.out_channels)
         return out

@@ -116,6 +116,15 @@ def gemm(A: Tensor, B: Tensor, bias: Optional[Tensor], out: Tensor, epilogue: in
     return out
 
 
+def unpatchify(tokens: Tensor, out: Tensor, p: int):
+    """tokens fp32 [R, T, p*p*C] -> out fp32 [R, C, H, W] (index map only)."""
+    L.require_cuda(tokens, out)
+    R, C, H, W = out.shape
+    assert tokens.dtype == torch.float32 and out.dtype == torch.float32 and tokens.is_contiguous() and out.is_contiguous()
+    L.check(L.lib().fitb200_unpatchify(L.ptr(tokens), R, tokens.shape[1], C, H, W, p, L.ptr(out), L.stream_ptr()), "unpatchify")
+    return out
+
+
 def gemm_stats_parts(N: int) -> int:
     """Partial sums per row that a GATE_RESID GEMM with N output columns writes through ``stats_out``."""
     return int(L.lib().fitb200_gemm_stats_parts(N))

@@ -79,12 +79,14 @@ class CFGSampler:
         """Number of libfit_b200 kernel launches in one step: 7 per block (un-fused: 2 ln_modulate + 4 GEMMs + attention; LN prologue: 2 small
         c-vector GEMMs + 4 GEMMs + attention) + embed / conditioning / final (8) + 4 loop kernels, + row_stats when the residual stream's
         row sums come from the GEMM epilogues (bf16 default), + modulation_pack when the LayerNorm prologue is active."""
-        from .engine import ln_prologue_ok, ln_stats_ok
+        from .engine import final_gemm_ok, ln_prologue_ok, ln_stats_ok
         L = len(self.model.blocks)
         prec, D = self.model.engine.precision, self.model.hidden_size
         fused = ln_prologue_ok(prec, 2 * self.B * self.T, D, self.T) and L > 0
         stats = fused or ln_stats_ok(prec, D)       # row_stats after the embedder; modulation_pack only with the prologue
-        return 7 * L + 8 + 4 + (1 if fused else 0) + (1 if stats else 0)
+        # final layer as a prologue GEMM: modulation_pack + c-vector GEMM + GEMM + unpatchify instead of the one CUDA-core kernel
+        fin = 3 if stats and final_gemm_ok(prec, 2 * self.B * self.T, D, self.T) else 0
+        return 7 * L + 8 + 4 + (1 if fused else 0) + (1 if stats else 0) + fin
 
     def noise_for_step(self, i: int, row_offset: int = 0, rows: Optional[int] = None) -> Tensor:
         rows = self.B if rows is None else rows

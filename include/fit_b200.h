@@ -185,6 +185,10 @@ int fitb200_final_layer_fwd(const void* x, int x_dtype, int R, int T, int D, con
                             int64_t ld_mod, const float* w, const float* b, int P, float* out, int out_nchw, int C,
                             int H, int W, int p, fitb200_stream_t stream);
 
+/* FiT.unpatchify (fit.py:444-456) alone: tokens fp32 [R, T, p*p*C] -> latents fp32 [R, C, H, W], T = (H/p)*(W/p).  (The bf16 engine's final
+ * layer is a tensor-core GEMM with the LayerNorm prologue that writes tokens; fitb200_final_layer_fwd fuses the map itself.) */
+int fitb200_unpatchify(const float* tokens, int R, int T, int C, int H, int W, int p, float* out, fitb200_stream_t stream);
+
 /* ---- diffusion step ------------------------------------------------------------------------------
  * coef: device fp32 table [S, 8] per (respaced) timestep:
  *   0 sqrt_recip_alphas_cumprod   1 sqrt_recipm1_alphas_cumprod   2 posterior_mean_coef1

