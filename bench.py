@@ -324,8 +324,14 @@ def kernel_rooflines(model, sampler, peaks, iters=10):
     p_, Cin = model.patch_size, model.in_channels
     add("embed_tokens", lambda: ops.embed_tokens(sampler.x, W.x_w, W.x_b, ws.xs, R, T, p_, Cin), 0.0, sampler.x.numel() * 4 + M * D * bpe)
     fsh, fsc = ws.fin_views
-    add("final_layer", lambda: ops.final_layer(ws.xs, fsh, fsc, W.n_mod, W.fin_w, W.fin_b, sampler.raw, R, T, p_, model.out_channels), 0.0,
-        M * D * bpe + sampler.raw.numel() * 4)
+    if getattr(ws, "fin_mod", None) is not None and ws.fin_c is not None:
+        # the engine's final layer: tcgen05 GEMM with the LayerNorm + modulate prologue, 16 output columns (one pass over the residual stream)
+        from fit_b200.engine import LN_EPS as _EPS
+        add("final_layer[ln+gemm N=16]", lambda: ops.gemm(ws.xs, W.fin_w16, None, ws.fin_tok, EPI_BIAS, rows_per_sample=T,
+                                                          ln=(ws.fin_mod[0, :R], ws.fin_c, ws.parts, _EPS)), 0.0, M * D * bpe + ws.fin_tok.numel() * 4)
+    else:
+        add("final_layer", lambda: ops.final_layer(ws.xs, fsh, fsc, W.n_mod, W.fin_w, W.fin_b, sampler.raw, R, T, p_, model.out_channels), 0.0,
+            M * D * bpe + sampler.raw.numel() * 4)
     add("philox_normal", lambda: ops.philox_normal(sampler.noise, 1234, sampler.t_idx, sampler.row_offset_dev), 0.0, sampler.noise.numel() * 4)
     tag = traffic_tag()
     for k, b in ncu_traffic(tag).items():
