@@ -5,6 +5,7 @@
 #include <cstdarg>
 
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -643,6 +644,34 @@ static void launch_ln(const void* x, int M, int D, int rows_per_sample, const fl
 #undef FITB200_LN_CASE
 }
 
+// ---------------------------------------------------------------------------------------------
+// fitb200_ln_modulate_fwd_static: scratch that lives in the library image instead of a caller / allocator buffer
+// ---------------------------------------------------------------------------------------------
+// Partial row sums (sum x, sum x^2) of up to FITB200_STATIC_LN_MAX_ROWS rows: 1 MiB per GPU that loads the library, held until exit.
+// Every call shares it (it keeps the last call's contents; nothing in it needs to start at zero: row_stats overwrites each entry the
+// following ln_apply reads).  Calls that overlap on one GPU (two streams) race on it.
+static __device__ __align__(256) float2 g_static_ln_parts[FITB200_STATIC_LN_MAX_ROWS];
+
+// The array's name is a host-side stand-in in host code, not a device address: its address is looked up once per device, with that device
+// current, and the POINTER is what the kernels receive.
+static int static_ln_parts_ptr(float2** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static float2* ptrs[MAX_DEV] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) { set_last_error("ln_modulate_fwd_static: cudaGetDevice failed or device index %d out of range", dev); return FITB200_ERR_CUDA; }
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    float2* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_static_ln_parts);
+    if (e != cudaSuccess || ptr == nullptr) { set_last_error("ln_modulate_fwd_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
+    ptrs[dev] = ptr;
+  }
+  *out = ptrs[dev];
+  return FITB200_OK;
+}
+
 }  // namespace fitb200
 
 using namespace fitb200;
@@ -963,6 +992,28 @@ int fitb200_unpatchify(const float* tokens, int R, int T, int C, int H, int W, i
   FITB200_CHECK_ARG(tokens && out && R > 0 && C > 0 && p > 0 && H % p == 0 && W % p == 0 && (H / p) * (W / p) == T, "unpatchify: inconsistent shape");
   unpatchify_kernel<<<step_grid((long)R * C * H * W), 256, 0, (cudaStream_t)stream>>>(tokens, R, T, C, H, W, p, out);
   FITB200_CHECK_LAUNCH("unpatchify");
+  return FITB200_OK;
+}
+
+int fitb200_ln_modulate_fwd_static(const void* x, int x_dtype, int M, int D, int rows_per_sample, const float* shift, const float* scale,
+                                   int64_t ld_mod, void* out, int out_dtype, fitb200_stream_t stream) {
+  FITB200_CHECK_ARG(x && shift && scale && out && M > 0 && rows_per_sample > 0, "ln_modulate_fwd_static: bad arguments");
+  FITB200_CHECK_ARG(M <= FITB200_STATIC_LN_MAX_ROWS, "ln_modulate_fwd_static: M=%d rows exceed the static scratch of %d rows (use fitb200_ln_modulate_fwd)",
+                    M, FITB200_STATIC_LN_MAX_ROWS);
+  FITB200_CHECK_ARG(D % 8 == 0 && ld_mod % 4 == 0 && ((uintptr_t)shift & 15) == 0 && ((uintptr_t)scale & 15) == 0,
+                    "ln_modulate_fwd_static: D=%d must be a multiple of 8, shift / scale 16-byte aligned", D);
+  float2* parts = nullptr;
+  const int rc = static_ln_parts_ptr(&parts);
+  if (rc != FITB200_OK) return rc;
+  const cudaStream_t s = (cudaStream_t)stream;
+  FITB200_DISPATCH_ACT(x_dtype, InT, {
+    row_stats_kernel<InT><<<(unsigned)ceil_div(M, 8), 256, 0, s>>>((const InT*)x, M, D, parts, 1);
+    FITB200_DISPATCH_ACT(out_dtype, OutT, {
+      ln_apply_kernel<InT, OutT><<<(unsigned)ceil_div(M, LNA_ROWS), 256, 0, s>>>((const InT*)x, M, D, rows_per_sample, parts, 1, 1e-6f, shift, scale,
+                                                                                ld_mod, (OutT*)out);
+    })
+  })
+  FITB200_CHECK_LAUNCH("ln_modulate_fwd_static");
   return FITB200_OK;
 }
 

@@ -177,6 +177,16 @@ int fitb200_attn_bwd(const void* qkv, int dtype, const float* freqs, int freqs_r
 int fitb200_ln_apply_fwd(const void* x, int x_dtype, int M, int D, int rows_per_sample, const float* parts, int nparts, float eps,
                          const float* shift, const float* scale, int64_t ld_mod, void* out, int out_dtype, fitb200_stream_t stream);
 
+/* fitb200_ln_modulate_fwd without ANY caller- or allocator-provided scratch.  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same
+ * result as fitb200_ln_modulate_fwd (eps 1e-6; no mean / rstd outputs): the row sums go through a file-scope `static __device__` array of
+ * FITB200_STATIC_LN_MAX_ROWS entries (1 MiB per GPU that loads the library, held until exit) and a streaming modulate pass.  M beyond that
+ * limit returns FITB200_ERR_INVALID_ARG.  The entry point calls no cudaMalloc / cudaFree / allocating routine.  All calls on one GPU share
+ * the array (it keeps the last call's contents; nothing in it has to start at zero): calls that overlap on the GPU (different streams) RACE. */
+#define FITB200_STATIC_LN_MAX_ROWS 131072
+int fitb200_ln_modulate_fwd_static(const void* x, int x_dtype, int M, int D, int rows_per_sample, const float* shift, const float* scale,
+                                   int64_t ld_mod, void* out, int out_dtype, fitb200_stream_t stream);
+
 /* ---- final layer ---------------------------------------------------------------------------------
  * FinalLayer.forward (dit.py:138-142) after its adaLN Linear: LN + modulate + Linear(D -> P) with
  * P = p*p*C_out, optionally fused with FiT.unpatchify (fit.py:444-456).
