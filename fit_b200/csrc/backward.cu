@@ -4,6 +4,8 @@
 //   bias-gradient column sums, SiLU, label-embedding scatter (fit.py:114), masked MSE (FiT/train.py:63-66), dtype casts.
 // Activations and activation gradients are T (bf16 or fp32); statistics, modulation tables, reductions and parameter gradients
 // are fp32.  Reductions over tokens use fp32 atomics into zero-initialised buffers (the caller zeroes them).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace fitb200 {
@@ -44,7 +46,10 @@ __global__ void __launch_bounds__(256) gate_bwd_kernel(const T* __restrict__ dx,
   if (live) {
     const Vec8<float> g = Vec8<float>::load(gate + (size_t)s * ld_gate + c);
 #pragma unroll 4
-    for (int t = rl; t < rps; t += CR_LANES) {
+    // gridDim.z row chunks per sample (when one CTA per (256 columns, sample) leaves most SMs idle: 160 CTAs at 32 samples x 1152 columns ran at
+    // 18 % of the HBM rate); the chunks' partial sums then meet in atomicAdds, gridDim.z per address
+    const int t_lo = (int)((long)rps * blockIdx.z / gridDim.z), t_hi = (int)((long)rps * (blockIdx.z + 1) / gridDim.z);
+    for (int t = t_lo + rl; t < t_hi; t += CR_LANES) {
       const size_t off = ((size_t)s * rps + t) * D + c;
       const Vec8<T> d = Vec8<T>::load(dx + off), yy = Vec8<T>::load(y + off);
       Vec8<T> o;
@@ -66,8 +71,10 @@ __global__ void __launch_bounds__(256) gate_bwd_kernel(const T* __restrict__ dx,
       float v = 0.f;
 #pragma unroll
       for (int r = 0; r < CR_LANES; ++r) v += red[r][g2][e];
-      if (e < 8) dgate[(size_t)s * ld_dgate + col] += v;   // this CTA owns (sample, column): plain read-modify-write
-      else if (dbias) atomicAdd(dbias + col, v);
+      if (e < 8) {
+        if (gridDim.z == 1) dgate[(size_t)s * ld_dgate + col] += v;   // this CTA owns (sample, column): plain read-modify-write
+        else atomicAdd(dgate + (size_t)s * ld_dgate + col, v);
+      } else if (dbias) atomicAdd(dbias + col, v);
     }
   }
 }
@@ -175,7 +182,8 @@ __global__ void __launch_bounds__(256) mod_bwd_cols_kernel(const T* __restrict__
   float a1[8] = {}, a2[8] = {};
   if (live) {
 #pragma unroll 4
-    for (int t = rl; t < rps; t += CR_LANES) {
+    const int t_lo = (int)((long)rps * blockIdx.z / gridDim.z), t_hi = (int)((long)rps * (blockIdx.z + 1) / gridDim.z);   // see gate_bwd_kernel
+    for (int t = t_lo + rl; t < t_hi; t += CR_LANES) {
       const size_t row = (size_t)s * rps + t;
       const float mu = mean[row], rs = rstd[row];
       const Vec8<T> d = Vec8<T>::load(dh + row * D + c), a = Vec8<T>::load(x + row * D + c);
@@ -193,7 +201,7 @@ __global__ void __launch_bounds__(256) mod_bwd_cols_kernel(const T* __restrict__
 #pragma unroll
       for (int r = 0; r < CR_LANES; ++r) v += red[r][g2][e];
       float* dst = (e < 8 ? dshift : dscale) + (size_t)s * ld_mod + col;
-      *dst += v;
+      if (gridDim.z == 1) *dst += v; else atomicAdd(dst, v);
     }
   }
 }
@@ -208,6 +216,35 @@ __global__ void colsum_kernel(const T* __restrict__ a, int M, int N, long lda, i
 #pragma unroll 8
   for (int m = m0; m < m1; ++m) s += to_f32(a[(size_t)m * lda + n]);
   atomicAdd(out + n, s);
+}
+
+// The same with 16-byte loads: CTA = 32 column groups of 8 x 8 row lanes over one row chunk, row lanes reduced through shared memory, one
+// atomicAdd per (chunk, column).  (The thread-per-column kernel above reads 2 bytes per thread and row: 18 % of the HBM rate on dqkv.)
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_vec_kernel(const T* __restrict__ a, int M, int N, long lda, int rows_per_chunk, float* __restrict__ out) {
+  __shared__ float red[CR_LANES][32][9];
+  const int cgl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = (blockIdx.x * 32 + cgl) * 8;
+  const int m0 = blockIdx.y * rows_per_chunk, m1 = min(M, m0 + rows_per_chunk);
+  float acc[8] = {};
+  if (c < N) {
+#pragma unroll 4
+    for (int m = m0 + rl; m < m1; m += CR_LANES) {
+      const Vec8<T> v = Vec8<T>::load(a + (size_t)m * lda + c);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += v.v[e];
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[rl][cgl][e] = acc[e];
+  __syncthreads();
+  const int g2 = threadIdx.x >> 3, e = threadIdx.x & 7, col = (blockIdx.x * 32 + g2) * 8 + e;
+  if (col < N) {
+    float v = 0.f;
+#pragma unroll
+    for (int r = 0; r < CR_LANES; ++r) v += red[r][g2][e];
+    atomicAdd(out + col, v);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ small pointwise pieces
@@ -280,6 +317,17 @@ static inline int grid_for(long n, int block, int cap = 148 * 16) {
 }
 // enough CTAs for ~4 waves without tiny chunks.  More, smaller chunks were measured slower (gate_bwd 2.4 -> 4.7 ms per XL/2 step): every
 // chunk ends in atomicAdds on the same dgate / dbias addresses, and those, not the row loop, bound these kernels.
+// row chunks per sample for the column-reduction kernels: enough CTAs for ~4 per SM, at least 4 rows per row lane
+static inline int row_chunks(long ctas, int rows_per_sample) {
+  static const int force = [] { const char* e = getenv("FITB200_BWD_ROW_CHUNKS"); return e ? atoi(e) : 0; }();
+  if (force > 0) return force;
+  long nz = (148L * 4 + ctas - 1) / ctas;
+  const long cap = rows_per_sample / (CR_LANES * 4);
+  if (nz > cap) nz = cap;
+  if (nz > 16) nz = 16;
+  return nz < 1 ? 1 : (int)nz;
+}
+
 static inline int chunk_rows(int rows, long other_ctas) {
   int chunks = (int)((148L * 4 + other_ctas - 1) / other_ctas);
   if (chunks < 1) chunks = 1;
@@ -309,7 +357,7 @@ int fitb200_gate_resid_fwd(const void* resid, const void* y, int dtype, const fl
 int fitb200_gate_bwd(const void* dx, const void* y, int dtype, const float* gate, int64_t ld_gate, int R, int rows_per_sample, int D,
                      void* dy, float* dgate, int64_t ld_dgate, float* dbias, fitb200_stream_t stream) {
   FITB200_CHECK_ARG(dx && y && gate && dy && dgate && R > 0 && rows_per_sample > 0 && D % 8 == 0 && ld_gate % 4 == 0, "gate_bwd: bad arguments");
-  dim3 grid(ceil_div(D / 8, 32), R);
+  dim3 grid(ceil_div(D / 8, 32), R, row_chunks(ceil_div(D / 8, 32) * R, rows_per_sample));
   FITB200_DISPATCH_ACT(dtype, T, {
     gate_bwd_kernel<T><<<grid, 256, 0, BW_STREAM>>>((const T*)dx, (const T*)y, gate, ld_gate, D, rows_per_sample, (T*)dy, dgate, ld_dgate, dbias);
   })
@@ -350,7 +398,7 @@ int fitb200_ln_modulate_bwd(const void* dh, const void* x, int dtype, const floa
   FITB200_CHECK_LAUNCH("ln_bwd_rows");
   if (dshift && dscale) {
     const int R = M / rows_per_sample;
-    dim3 grid(ceil_div(D / 8, 32), R);
+    dim3 grid(ceil_div(D / 8, 32), R, row_chunks(ceil_div(D / 8, 32) * R, rows_per_sample));
     FITB200_DISPATCH_ACT(dtype, T, {
       mod_bwd_cols_kernel<T><<<grid, 256, 0, BW_STREAM>>>((const T*)dh, (const T*)x, mean, rstd, D, rows_per_sample, dshift, dscale, ld_dmod);
     })
@@ -361,6 +409,16 @@ int fitb200_ln_modulate_bwd(const void* dh, const void* x, int dtype, const floa
 
 int fitb200_colsum(const void* a, int dtype, int M, int N, int64_t lda, float* out, fitb200_stream_t stream) {
   FITB200_CHECK_ARG(a && out && M > 0 && N > 0, "colsum: bad arguments");
+  if (N % 8 == 0 && lda % 8 == 0 && ((uintptr_t)a & 15) == 0 && M >= 64) {
+    const int bx = ceil_div(N / 8, 32);
+    int rpc = chunk_rows(M, bx);
+    rpc = (rpc + CR_LANES - 1) / CR_LANES * CR_LANES;
+    if (rpc < 4 * CR_LANES) rpc = 4 * CR_LANES;
+    dim3 grid(bx, ceil_div(M, rpc));
+    FITB200_DISPATCH_ACT(dtype, T, { colsum_vec_kernel<T><<<grid, 256, 0, BW_STREAM>>>((const T*)a, M, N, lda, rpc, out); })
+    FITB200_CHECK_LAUNCH("colsum");
+    return FITB200_OK;
+  }
   const int bx = ceil_div(N, 128);
   const int rpc = chunk_rows(M, bx);
   dim3 grid(bx, ceil_div(M, rpc));

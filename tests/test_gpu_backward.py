@@ -101,6 +101,14 @@ def test_small_backward_pieces(ops):
     assert rel_l2(out, a[:, :136].double().sum(0)) < 1e-5
     outb = ops.colsum(a.bfloat16().cuda(), torch.zeros(200, device="cuda"))
     assert rel_l2(outb, a.bfloat16().double().sum(0)) < 1e-5
+    # vectorised path at a training shape (ragged last row chunk), the thread-per-column path for widths / strides that are not multiples of 8,
+    # accumulation into a non-zero output
+    big = torch.randn(8200, 3456, generator=g).bfloat16()
+    outv = ops.colsum(big.cuda(), torch.ones(3456, device="cuda"))
+    assert rel_l2(outv, big.double().sum(0) + 1.0) < 1e-5
+    odd = torch.randn(300, 203, generator=g)
+    outo = ops.colsum(odd.cuda()[:, :13], torch.zeros(13, device="cuda"))
+    assert rel_l2(outo, odd[:, :13].double().sum(0)) < 1e-5
     x = torch.randn(7, 144, generator=g).double().requires_grad_(True)
     dy = torch.randn(7, 144, generator=g)
     F.silu(x).backward(dy.double())
