@@ -79,6 +79,14 @@ __global__ void __launch_bounds__(256) gate_bwd_kernel(const T* __restrict__ dx,
   }
 }
 
+// sigmoid for the SwiGLU kernels: exact expf / division for fp32 storage (verification mode), the fast intrinsics for bf16 storage (their
+// error, ~2 ulp fp32, is far below the bf16 rounding of the result; with expf + IEEE division these kernels were issue-bound: 75 % issue
+// slots busy at 41 % of the HBM rate)
+template <typename T> __device__ __forceinline__ float sigmoid_t(float x) {
+  if constexpr (sizeof(T) == 2) return __fdividef(1.0f, 1.0f + __expf(-x));
+  else return 1.0f / (1.0f + expf(-x));
+}
+
 // ------------------------------------------------------------------------------------------------ SwiGLU forward / backward
 // u [M, 2*Hp]: every 32 columns = 16 gate pre-activations then the matching 16 up pre-activations (the packed fc1 weight).
 template <typename T>
@@ -91,7 +99,7 @@ __global__ void swiglu_fwd_kernel(const T* __restrict__ u, int M, int Hp, T* __r
     const Vec8<T> a = Vec8<T>::load(u + uo), b = Vec8<T>::load(u + uo + 16);
     Vec8<T> o;
 #pragma unroll
-    for (int e = 0; e < 8; ++e) o.v[e] = silu_acc(a.v[e]) * b.v[e];
+    for (int e = 0; e < 8; ++e) o.v[e] = a.v[e] * sigmoid_t<T>(a.v[e]) * b.v[e];
     o.store(g + (size_t)m * Hp + j * 8);
   }
 }
@@ -112,7 +120,7 @@ __global__ void swiglu_bwd_kernel(const T* __restrict__ dg, const T* __restrict_
     Vec8<T> oa, ob;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const float sg = 1.0f / (1.0f + expf(-a.v[e]));
+      const float sg = sigmoid_t<T>(a.v[e]);
       const float si = a.v[e] * sg;
       oa.v[e] = d.v[e] * b.v[e] * (sg * (1.0f + a.v[e] * (1.0f - sg)));
       ob.v[e] = d.v[e] * si;
@@ -128,30 +136,59 @@ __global__ void swiglu_bwd_kernel(const T* __restrict__ dg, const T* __restrict_
 
 // ------------------------------------------------------------------------------------------------ LayerNorm + modulate backward
 // rows: dxhat = dh * (1 + scale[s]);  dx = rstd * (dxhat - mean(dxhat) - xhat * mean(dxhat * xhat)) + dres.  One warp per row.
+// 8 consecutive elements as loaded (16 bytes of bf16 / 32 bytes of fp32): rows are kept packed between the two passes of ln_bwd_rows
+template <typename T> struct Pack8;
+template <> struct Pack8<__nv_bfloat16> {
+  uint4 r;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { r = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void get(float (&f)[8]) const {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float2 t = __bfloat1622float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+  }
+};
+template <> struct Pack8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) { a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 4); }
+  __device__ __forceinline__ void get(float (&f)[8]) const { f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w; }
+};
+
+// All three inputs of a row (x, dh, dres) are requested up front (one exposed memory latency per row instead of two) and kept PACKED between
+// the statistics pass and the output pass (the fp32 copies cost 98 registers: two CTAs per SM, 22 % of the HBM rate).
 template <typename T, int NV>
-__global__ void __launch_bounds__(256) ln_bwd_rows_kernel(const T* __restrict__ dh, const T* __restrict__ x, const float* __restrict__ mean,
+__global__ void __launch_bounds__(256, 2) ln_bwd_rows_kernel(const T* __restrict__ dh, const T* __restrict__ x, const float* __restrict__ mean,
                                                           const float* __restrict__ rstd, const float* __restrict__ scale, long ld_mod,
                                                           int M, int D, int rps, const T* __restrict__ dres, T* __restrict__ dx) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= M) return;
   const int nvec = D >> 3;
-  const float mu = mean[row], rs = rstd[row];
   const float* sc = scale + (size_t)(row / rps) * ld_mod;
-  float xh[NV][8], dxh[NV][8];
+  constexpr bool EARLY = sizeof(T) == 2;   // (fp32 rows: three packed copies do not fit the register file; dres is loaded in the output pass)
+  Pack8<T> px[NV], pd[NV], pr[EARLY ? NV : 1];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vi = lane + i * 32;
+    if (vi < nvec) {
+      px[i].load(x + (size_t)row * D + vi * 8);
+      pd[i].load(dh + (size_t)row * D + vi * 8);
+      if (EARLY && dres) pr[i].load(dres + (size_t)row * D + vi * 8);
+    }
+  }
+  const float mu = mean[row], rs = rstd[row];
   float s1 = 0.f, s2 = 0.f;
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int vi = lane + i * 32;
     if (vi < nvec) {
-      const Vec8<T> a = Vec8<T>::load(x + (size_t)row * D + vi * 8), d = Vec8<T>::load(dh + (size_t)row * D + vi * 8);
+      float a[8], d[8];
+      px[i].get(a); pd[i].get(d);
       const Vec8<float> s = Vec8<float>::load(sc + vi * 8);
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
-        xh[i][e] = (a.v[e] - mu) * rs;
-        dxh[i][e] = d.v[e] * (1.0f + s.v[e]);
-        s1 += dxh[i][e];
-        s2 = fmaf(dxh[i][e], xh[i][e], s2);
+        const float dxh = d[e] * (1.0f + s.v[e]);
+        s1 += dxh;
+        s2 = fmaf(dxh, (a[e] - mu) * rs, s2);
       }
     }
   }
@@ -161,10 +198,16 @@ __global__ void __launch_bounds__(256) ln_bwd_rows_kernel(const T* __restrict__ 
   for (int i = 0; i < NV; ++i) {
     const int vi = lane + i * 32;
     if (vi < nvec) {
+      float a[8], d[8], r[8];
+      px[i].get(a); pd[i].get(d);
+      if (dres) {
+        if (!EARLY) pr[0].load(dres + (size_t)row * D + vi * 8);
+        pr[EARLY ? i : 0].get(r);
+      }
+      const Vec8<float> s = Vec8<float>::load(sc + vi * 8);   // an L1 hit: read by the statistics pass just above
       Vec8<T> o;
-      if (dres) o = Vec8<T>::load(dres + (size_t)row * D + vi * 8);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) o.v[e] = (dres ? o.v[e] : 0.f) + rs * (dxh[i][e] - s1 - xh[i][e] * s2);
+      for (int e = 0; e < 8; ++e) o.v[e] = (dres ? r[e] : 0.f) + rs * (d[e] * (1.0f + s.v[e]) - s1 - (a[e] - mu) * rs * s2);
       o.store(dx + (size_t)row * D + vi * 8);
     }
   }
