@@ -12,6 +12,7 @@ block, 9.5 GB in all -- nothing is recomputed.
 from __future__ import annotations
 
 import math
+import os
 from typing import Callable, Dict, List, Optional
 
 import torch
@@ -132,6 +133,13 @@ class FiTTrainEngine:
     @property
     def act(self):
         return torch.bfloat16 if self.precision == "bf16" else torch.float32
+
+    def _side_stream(self, dev):
+        st = getattr(self, "_side", None)
+        if st is None or st.device != torch.device(dev):
+            st = torch.cuda.Stream(device=dev)
+            self._side = st
+        return st
 
     def _key(self):
         return (self.precision,) + tuple((p.data_ptr(), p._version) for p in self.model.parameters())
@@ -265,6 +273,31 @@ class FiTTrainEngine:
         def wgrad(dy: Tensor, x: Tensor, out: Optional[Tensor] = None) -> Tensor:           # dW[N, K] = dy[M, N]^T x[M, K]
             return ops.gemm(dy, x, None, torch.empty(dy.shape[1], x.shape[1], **f32) if out is None else out, EPI_BIAS, a_mn=True, b_mn=True)
 
+        # The weight-gradient GEMMs of a block run on a SIDE stream next to the dgrad chain: at 8192 token rows the persistent GEMM grids end in
+        # partial waves (proj / fc2 dgrad: 160 tiles on 74 CTA pairs = 2.16 waves; dW_proj: 25 tiles = a third of the GPU), and a second kernel's
+        # CTAs start on the SMs the first one has left.  Nothing downstream reads a weight gradient before the block's buckets are handed over,
+        # so the side stream is joined once per block.  Tensors it reads are kept alive until that join (`keep`): the caching allocator may
+        # hand a freed block to the main stream only after the join has ordered the two streams.  FITB200_TRAIN_WGRAD_STREAM=0 switches it off.
+        main_stream = torch.cuda.current_stream(dev)
+        side = self._side_stream(dev) if os.environ.get("FITB200_TRAIN_WGRAD_STREAM", "1") != "0" else None
+        keep: List[Tensor] = []
+
+        class _Side:
+            def __enter__(_s):
+                if side is not None:
+                    side.wait_stream(main_stream)          # everything queued so far (the dy this wgrad reads) is ordered before it
+                    _s.ctx = torch.cuda.stream(side)
+                    _s.ctx.__enter__()
+
+            def __exit__(_s, *a):
+                if side is not None:
+                    _s.ctx.__exit__(*a)
+
+        def join_side():
+            if side is not None:
+                main_stream.wait_stream(side)
+            keep.clear()
+
         def bucket(shapes):
             """One flat fp32 buffer holding the listed gradients back to back (16-byte aligned offsets): the data-parallel all-reduce runs
             on it in place -- no packing copy before and no scatter copy after the collective.  Only the vectors (bias gradients, accumulated
@@ -320,17 +353,23 @@ class FiTTrainEngine:
             # x_out = x_mid + gate_mlp * fc2(g)
             dy2 = ops.gate_bwd(dx, b.y2, mv[5], nm, R, T, torch.empty(M, D, **a), dv[5], nm, g_fc2b)
             grads[pre + "ffn.fc2.bias"] = g_fc2b
-            if Hp != H:
-                g_fc2w.copy_(wgrad(dy2, b.g)[:, :H])
-            else:
-                wgrad(dy2, b.g, g_fc2w)
+            with _Side():
+                if Hp != H:
+                    tmp = wgrad(dy2, b.g)
+                    g_fc2w.copy_(tmp[:, :H])
+                    keep.append(tmp)
+                else:
+                    wgrad(dy2, b.g, g_fc2w)
+            keep.extend([dy2, b.g])
             grads[pre + "ffn.fc2.weight"] = g_fc2w
             dg = dgrad(dy2, e["fc2_w"])
             # g = silu(u_gate) * u_up
             db1 = torch.zeros(2 * Hp, **f32)
             du = ops.swiglu_bwd(dg, b.u, torch.empty(M, 2 * Hp, **a), db1)
-            dw1 = wgrad(du, b.h2).view(Hp // 16, 2, 16, D)
-            g_f1gw.copy_(dw1[:, 0].reshape(Hp, D)[:H]); g_f1xw.copy_(dw1[:, 1].reshape(Hp, D)[:H])   # un-interleave the packed fc1 rows
+            with _Side():
+                dw1 = wgrad(du, b.h2).view(Hp // 16, 2, 16, D)
+                g_f1gw.copy_(dw1[:, 0].reshape(Hp, D)[:H]); g_f1xw.copy_(dw1[:, 1].reshape(Hp, D)[:H])   # un-interleave the packed fc1 rows
+            keep.extend([du, b.h2, dw1])
             grads[pre + "ffn.fc1_g.weight"], grads[pre + "ffn.fc1_x.weight"] = g_f1gw, g_f1xw
             db1 = db1.view(Hp // 16, 2, 16)
             g_f1gb.copy_(db1[:, 0].reshape(Hp)[:H]); g_f1xb.copy_(db1[:, 1].reshape(Hp)[:H])
@@ -340,11 +379,15 @@ class FiTTrainEngine:
             # x_mid = x_in + gate_msa * proj(att)
             dy1 = ops.gate_bwd(dx_mid, b.y1, mv[2], nm, R, T, torch.empty(M, D, **a), dv[2], nm, g_pb)
             grads[pre + "attn.proj.bias"] = g_pb
-            grads[pre + "attn.proj.weight"] = wgrad(dy1, b.att, g_pw)
+            with _Side():
+                grads[pre + "attn.proj.weight"] = wgrad(dy1, b.att, g_pw)
+            keep.extend([dy1, b.att])
             datt = dgrad(dy1, e["proj_w"])
             dqkv = ops.attention_bwd(b.qkv, S.pos, S.kv_len, S.mask, R, T, h, d, b.att, datt, b.lse, torch.empty(M, 3 * D, **a), prerotated=bf16)
             grads[pre + "attn.qkv.bias"] = ops.colsum(dqkv, g_qb)
-            grads[pre + "attn.qkv.weight"] = wgrad(dqkv, b.h1, g_qw)
+            with _Side():
+                grads[pre + "attn.qkv.weight"] = wgrad(dqkv, b.h1, g_qw)
+            keep.extend([dqkv, b.h1])
             dh1 = dgrad(dqkv, e["qkv_w"])
             dx = ops.ln_modulate_bwd(dh1, b.x_in, b.mean1, b.rstd1, mv[1], nm, T, dx_mid, torch.empty(M, D, **a), dv[0], dv[1], nm)
             # adaLN table of this block: mod_i = silu(c) W_i^T + b_i (fit.py:323-324,329).  Its six dmod chunks are final now, so the
@@ -353,6 +396,7 @@ class FiTTrainEngine:
             dmod_ia = dmod_i.contiguous() if act == torch.float32 else ops.cast(dmod_i.contiguous(), torch.empty(R, 6 * D, **a))
             grads[pre + "adaLN_modulation.1.weight"] = wgrad(dmod_ia, S.silu_c, g_aw)
             grads[pre + "adaLN_modulation.1.bias"] = ops.colsum(dmod_i, g_ab)
+            join_side()
             emit(pre[:-1], [pre + s for s in ("ffn.fc2.bias", "ffn.fc2.weight", "ffn.fc1_g.weight", "ffn.fc1_x.weight", "ffn.fc1_g.bias",
                                               "ffn.fc1_x.bias", "attn.proj.bias", "attn.proj.weight", "attn.qkv.bias", "attn.qkv.weight",
                                               "adaLN_modulation.1.weight", "adaLN_modulation.1.bias")], flat)
