@@ -217,6 +217,7 @@ def ncu_traffic(tag="r1f"):
     scale = lambda h: 1e9 if "Gbyte" in h else 1e6 if "Mbyte" in h else 1e3 if "Kbyte" in h else 1.0  # noqa: E731
     for r in rows[1:]:
         name, b = r[0], float(r[ir]) * scale(hdr[ir]) + float(r[iw]) * scale(hdr[iw])
+        name = name.replace("void ", "").replace("fitb200::", "")   # ncu prints the namespace for some kernels, not for others
         key = None
         lna = name.rstrip().endswith("1, 1>")   # LN-prologue instantiations
         if name.startswith("gemm_tc_kernel<256, 3"): key = "gemm_tc[ln+swiglu fc1_g|fc1_x]" if lna else "gemm_tc[swiglu fc1_g|fc1_x]"
