@@ -513,7 +513,7 @@ def run_cuda_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("FITB200_DDP_RESERVE_SMS", "8"))   # the DDP leg: NCCL stays inside the SMs GradSync leaves free
+        os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("FITB200_DDP_RESERVE_SMS") or ("16" if int(os.environ.get("WORLD_SIZE", "1")) > 2 else "8"))   # the DDP leg: NCCL stays inside the SMs GradSync leaves free
         # NCCL prints its version banner on STDOUT when the communicator is created (NCCL_DEBUG >= VERSION on the GPU boxes; WARN still
         # prints it).  stdout carries exactly one JSON line, so file descriptor 1 points at stderr while the communicator comes up.
         sys.stdout.flush()

@@ -12,7 +12,7 @@ from fit_b200.models.fit import FiT_models
 from fit_b200.rope import precompute_freqs_cis_2d
 from fit_b200.train import GradSync, masked_mse_loss
 
-os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("FITB200_DDP_RESERVE_SMS", "8"))   # NCCL stays inside the SMs GradSync leaves free
+os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("FITB200_DDP_RESERVE_SMS") or ("16" if int(os.environ.get("WORLD_SIZE", "1")) > 2 else "8"))   # NCCL stays inside the SMs GradSync leaves free
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
