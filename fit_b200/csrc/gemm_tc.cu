@@ -71,6 +71,8 @@ struct GtParams {
   int tail_rows;  // K-major B: rows of the narrower TMA box (tmBt) used for the last, cut column tile (0 = always the full box)
   int bias_row0;  // the bias is added to rows >= bias_row0 only (0 = every row)
   int epi_sleep;  // nanoseconds between the epilogue's polls of the accumulator-full barrier (0 = spin)
+  // split-K (wgrad GEMMs with few output tiles): work item = (tile, k-range); the partial tiles meet in TMA reduce-add stores on a zeroed output
+  int splits, kb_per_split;
   // LNA (LayerNorm + adaLN-modulate prologue, see the A-producer warps below)
   const __nv_bfloat16* lnx; long ld_lnx;   // raw residual-stream rows x [M, K]
   const __nv_bfloat16* lng; long ld_lng;   // bf16(1 + scale) [samples, K]
@@ -148,6 +150,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int tiles_n = ceil_div(p.N, BN), tiles_m = ceil_div(p.M, TM);
   const int num_tiles = tiles_m * tiles_n;
   const int num_kb = ceil_div(p.K, GT_BK);
+  const int nsplit = LNA ? 1 : p.splits;                       // host: every split is non-empty; 1 for everything but the wgrad GEMMs
+  const int num_items = num_tiles * nsplit;                    // item = split * num_tiles + tile
+  const int kbs = nsplit > 1 ? p.kb_per_split : num_kb;
   const uint32_t rank = PAIR ? ptx::cluster_ctarank() : 0u;   // 0 = leader: issues the MMAs of the pair
   const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;      // scheduling unit (CTA or pair)
   const int nwork = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
@@ -187,11 +192,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = wid; tile < num_tiles; tile += nwork) {
+      for (int item = wid; item < num_items; item += nwork) {
+        const int tile = item % num_tiles, kb0 = (item / num_tiles) * kbs, kb1 = min(num_kb, kb0 + kbs);
         // the last column tile may be narrower (MMA N = nn): in a pair the second CTA's half of B then starts nn / 2 rows in
         const int n0t = (tile % tiles_n) * BN, nn = min(BN, (p.N - n0t + NGRAN - 1) / NGRAN * NGRAN);
         const int m0 = (tile / tiles_n) * TM + row_off, n0 = n0t + (int)rank * (nn / 2);
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           if (PAIR) {
             // both CTAs' bytes are counted on the LEADER's full barrier (the only one the MMA thread waits on)
@@ -245,7 +251,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       constexpr uint32_t idesc0 = ptx::idesc_bf16_f32(TM, 0) | (AMN ? 1u << 15 : 0u) | (BMN ? 1u << 16 : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
-      for (int tile = wid; tile < num_tiles; tile += nwork, ++it) {
+      for (int item = wid; item < num_items; item += nwork, ++it) {
+        const int tile = item % num_tiles, kb0 = (item / num_tiles) * kbs, kb1 = min(num_kb, kb0 + kbs);
         const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
         // epilogue (of both CTAs of a pair) has drained this accumulator stage
         // (plain wait also for the pair: the peer's arrivals order no memory -- the hand-off is "TMEM drained", fenced by tcgen05 -- and a
@@ -258,7 +265,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // per flop are what grows)
         const int nn = min(BN, (p.N - (tile % tiles_n) * BN + NGRAN - 1) / NGRAN * NGRAN);
         const uint32_t idesc = idesc0 | ((uint32_t)(nn >> 3) << 17);
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           // (LNA: the A rows of both CTAs were published by their relay threads behind a generic -> async proxy fence.  NOT a cluster-scope
           // acquire here: it compiles to CCTL.IVALL -- an L1 invalidate per k-slab, which turned every spill reload and table read of the
           // other warps into an L2 round trip: the fused GEMMs ran 2.5x slower)
@@ -271,8 +278,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int k = 0; k < GT_BK / 16; ++k) {
             // 16 elements along K: K-major = 32 bytes inside the 128-byte swizzle row (+2 in the addr >> 4 field);
             // MN-major = 16 k-rows of 128 bytes (+128)
-            if (PAIR) ptx::mma_f16_ss_pair(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0);
-            else ptx::mma_f16_ss(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0);
+            if (PAIR) ptx::mma_f16_ss_pair(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, ((kb - kb0) | k) != 0);
+            else ptx::mma_f16_ss(d_tmem, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, ((kb - kb0) | k) != 0);
           }
           // smem slot reusable once these MMAs retire (pair: the slot of BOTH CTAs)
           if (PAIR) ptx::mma_commit_pair(&empty_bar[stage], 3); else ptx::mma_commit(&empty_bar[stage]);
@@ -380,7 +387,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int qbar = 1 + quarter;                // named barrier of this quarter's two warps
     constexpr int QROWS = 32, QBYTES = QROWS * 128;
     const uint32_t sw = (uint32_t)(row & 7); // 128B-swizzle phase of this row
-    const int my_tiles = wid < num_tiles ? (num_tiles - 1 - wid) / nwork + 1 : 0;
+    const int my_tiles = wid < num_items ? (num_items - 1 - wid) / nwork + 1 : 0;   // work items of this CTA (pair)
     const uint32_t tempty_leader = PAIR ? ptx::mapa(ptx::smem_u32(&tempty_bar[0]), 0) : 0u;  // the leader's tempty_bar[0]
     const int total_slabs = my_tiles * NSLAB;
 
@@ -390,7 +397,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #ifdef FITB200_TUNING
       if (p.dbg & 4) return;
 #endif
-      const int tile = wid + (qq / NSLAB) * nwork, slab = qq % NSLAB;
+      const int tile = (wid + (qq / NSLAB) * nwork) % num_tiles, slab = qq % NSLAB;
       const int rm0 = (tile / tiles_n) * TM + row_off, rn0 = (tile % tiles_n) * BN + slab * OUTC;
       ptx::mbar_arrive_expect_tx(&res_bar[quarter * 2 + (qq & 1)], QBYTES);
       ptx::tma_load_2d(smemRes + (qq & 1) * GT_SLAB_BYTES + quarter * QBYTES, &tmRes, &res_bar[quarter * 2 + (qq & 1)], rn0, rm0 + quarter * QROWS);
@@ -400,7 +407,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int q = 0;  // running slab index
     int rope_m0 = -1;  // key of the row block whose RoPE rows are in smemRope (token offset for a shared table, else the row block itself)
     for (int it = 0; it < my_tiles; ++it) {
-      const int tile = wid + it * nwork;
+      const int tile = (wid + it * nwork) % num_tiles;
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       const int m0 = (tile / tiles_n) * TM + row_off, n0 = (tile % tiles_n) * BN;
       const int m = min(m0 + row, p.M - 1);
@@ -636,7 +643,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         ptx::fence_proxy_async_smem();  // make the st.shared visible to the TMA (async proxy)
         ptx::named_bar_sync(qbar, 64);
         if (leader) {
-          if (live) ptx::tma_store_2d(&tmOut, smemOut + buf * GT_SLAB_BYTES + quarter * QBYTES, nout, m0 + quarter * QROWS);
+          if (live) {
+            if (nsplit > 1) ptx::tma_reduce_add_2d(&tmOut, smemOut + buf * GT_SLAB_BYTES + quarter * QBYTES, nout, m0 + quarter * QROWS);
+            else ptx::tma_store_2d(&tmOut, smemOut + buf * GT_SLAB_BYTES + quarter * QBYTES, nout, m0 + quarter * QROWS);
+          }
           ptx::tma_store_commit();
           if (RESID) issue_resid(q + 2);  // this residual buffer has been consumed by all 128 threads
         }
@@ -745,8 +755,35 @@ static int launch_tc(const fitb200_gemm_args& a, cudaStream_t s) {
     if (e != cudaSuccess) { set_last_error("gemm_bf16_tc: cannot set %d bytes of dynamic smem: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
     attr_done = true;
   }
+  p.splits = 1; p.kb_per_split = 0;
   if (PAIR) {
-    const int tiles = ceil_div(a.M, 2 * GT_BM) * ceil_div(a.N, BN);
+    int tiles = ceil_div(a.M, 2 * GT_BM) * ceil_div(a.N, BN);
+    if constexpr (AMN && BMN && sizeof(OutT) == 4 && EPI == FITB200_EPI_BIAS) {
+      // weight-gradient GEMMs (both operands contraction-major, fp32 output, no bias): few output tiles (dW_proj: 25 on 74 CTA pairs) over a
+      // long contraction (the token rows).  Split the contraction so that the work items fill whole waves; the partial tiles are ADDED into
+      // the zeroed output by TMA reduce stores (fp32 adds in arrival order: the last bits of a gradient may differ from run to run).
+      // FITB200_GEMM_SPLITK=0 switches it off.
+      // FITB200_GEMM_SPLITK: 0 = off, n >= 2 = force n splits (tuning), unset = cost model
+      static const int splitk = [] { const char* e = getenv("FITB200_GEMM_SPLITK"); return e ? atoi(e) : -1; }();
+      const int num_kb = ceil_div(a.K, GT_BK), slots = sm_count() / 2;
+      if (splitk != 0 && a.bias == nullptr && num_kb >= 32 && slots > 0) {
+        // cost of a schedule in k-slab times: waves x (k-slabs per item + the item's epilogue, ~12 k-slabs for a 256 x 256 fp32 tile that is
+        // not hidden behind a following mainloop)
+        auto cost = [&](int sp) { return (double)ceil_div(tiles * sp, slots) * ((double)ceil_div(num_kb, sp) + 12.0); };
+        int best = 1; double best_cost = cost(1);
+        for (int sp = 2; sp <= 8 && num_kb / sp >= 16; ++sp)
+          if (cost(sp) < 0.9 * best_cost) { best = sp; best_cost = cost(sp); }
+        if (splitk >= 2) best = splitk <= num_kb ? splitk : 1;
+        if (best > 1) {
+          const int kbs = ceil_div(num_kb, best);
+          p.splits = ceil_div(num_kb, kbs);          // every split non-empty
+          p.kb_per_split = kbs;
+          cudaError_t e = cudaMemset2DAsync(a.out, (size_t)a.ldo * sizeof(OutT), 0, (size_t)a.N * sizeof(OutT), (size_t)a.M, s);
+          if (e != cudaSuccess) { set_last_error("gemm_bf16_tc: split-K memset failed: %s", cudaGetErrorString(e)); return FITB200_ERR_CUDA; }
+          tiles *= p.splits;
+        }
+      }
+    }
     const int pairs = tiles < sm_count() / 2 ? tiles : sm_count() / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = Cfg::SMEM_BYTES; cfg.stream = s;

@@ -317,3 +317,21 @@ def test_gemm_ln_prologue_argument_errors(ops):
     out = torch.empty(400, 256, dtype=torch.bfloat16, device="cuda")
     with pytest.raises(RuntimeError, match="rows_per_sample"):   # CTA tiles would straddle samples: callers take the ln_modulate kernel
         ops.gemm(x.cuda(), W.cuda(), None, out, EPI_BIAS, rows_per_sample=200, ln=(g, c, parts, 1e-6))
+
+
+@pytest.mark.parametrize("Nout,Kin,tokens", [(1152, 1152, 8192), (768, 768, 4096), (1152, 3072, 8192)])
+def test_wgrad_split_k_matches_unsplit(ops, Nout, Kin, tokens, monkeypatch):
+    """Weight-gradient GEMMs with few output tiles split the token contraction into work items whose partial tiles are added into the zeroed fp32
+    output by TMA reduce stores (cost model in launch_tc; dW_proj at 8192 rows: 2 splits).  Against fp64 math on the same inputs, with a
+    NaN-filled output buffer (the entry point zeroes it itself)."""
+    g = torch.Generator().manual_seed(Nout + Kin)
+    dy = torch.randn(tokens, Nout, generator=g).bfloat16()
+    x = torch.randn(tokens, Kin, generator=g).bfloat16()
+    want = dy.double().t() @ x.double()
+    out = torch.full((Nout, Kin), float("nan"), device="cuda")
+    ops.gemm(dy.cuda(), x.cuda(), None, out, EPI_BIAS, a_mn=True, b_mn=True)
+    assert rel_l2(out, want) < 1e-5
+    # a strided output (a view into a gradient bucket row): only the view's columns are zeroed / written
+    big = torch.full((Nout, Kin + 64), 7.0, device="cuda")
+    ops.gemm(dy.cuda(), x.cuda(), None, big[:, :Kin], EPI_BIAS, a_mn=True, b_mn=True)
+    assert rel_l2(big[:, :Kin], want) < 1e-5 and float((big[:, Kin:] - 7.0).abs().max()) == 0.0
