@@ -13,8 +13,8 @@ mask = torch.zeros(R, T, dtype=torch.bool, device="cuda"); mask[:, :valid] = Tru
 kv, _ = ops.mask_to_kvlen(mask)
 out = torch.empty(R * T, h * d, device="cuda", dtype=torch.bfloat16)
 scratch = torch.empty(64 * 1024 * 1024, device="cuda")
-PRE = int(os.environ.get("PRE", 1))
-run = (lambda: ops.attention(qkv, None, kv, mask, R, T, h, d, out, prerotated=True)) if PRE else (lambda: ops.attention(qkv, pos, kv, mask, R, T, h, d, out))
+PRE = 1   # bf16 operands always carry the RoPE (the un-rotated bf16 kernels were removed in round 2)
+run = lambda: ops.attention(qkv, None, kv, mask, R, T, h, d, out, prerotated=True)
 for _ in range(3):
     run()
 torch.cuda.synchronize()
